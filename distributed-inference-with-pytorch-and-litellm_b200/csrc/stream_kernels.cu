@@ -1,0 +1,227 @@
+// Kernel (a) pack / unpack (+scale, +cast) and kernel (b) multi-tensor L2 norm.
+//
+// One persistent launch covers every segment of a bucket (or of the whole model). A CTA
+// takes chunk c, c+grid, c+2*grid, ...; a chunk is a contiguous run of one segment, so every
+// warp request is a fully coalesced 512-byte (fp32) / 512-byte (bf16) line set. Roofline: HBM.
+//   pack/unpack : s_src + s_dst bytes per element
+//   norm        : s bytes per element (read only)
+// The sum of squares, when asked for, is reduced warp-shuffle -> shared-memory tree -> one
+// float per chunk -> "last CTA" fold per segment (common.cuh), i.e. single pass, one launch.
+#include "launch.cuh"
+
+namespace ddpb200 {
+
+template <int SDT, int DDT> struct StreamGroup {
+  static constexpr int G = (SDT == DDPB200_F32 || DDT == DDPB200_F32) ? 4 : 8;
+  static constexpr int U = 8 / G;  // groups per thread per tile
+};
+
+// SRC / DST: which ptr[] slot is read / written. STORE=false -> norm only.
+template <class Tab, int SDT, int DDT, int SRC, int DST, bool STORE, bool NORM, bool DEVSCALE>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
+              float scale, const float* __restrict__ scale_ptr, float* __restrict__ sumsq_out,
+              float* __restrict__ chunk_partials, uint32_t* ticket) {
+  constexpr int G = StreamGroup<SDT, DDT>::G;
+  constexpr int U = StreamGroup<SDT, DDT>::U;
+  __shared__ float red[kThreads / 32];
+
+  if constexpr (DEVSCALE) scale = __ldg(scale_ptr);
+  const int64_t chunk_base = tab.begin(0);
+
+  for (int64_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+    const int s = find_seg(tab, c + chunk_base);
+    const int64_t start = (c + chunk_base - tab.begin(s)) * chunk_elems;
+    const int64_t rest = tab.numel(s) - start;
+    const int64_t len = rest < chunk_elems ? rest : chunk_elems;
+    const char* src = static_cast<const char*>(tab.ptr(s, SRC)) + start * ElemOf<SDT>::size;
+    char* dst = nullptr;
+    if constexpr (STORE) dst = static_cast<char*>(tab.ptr(s, DST)) + start * ElemOf<DDT>::size;
+
+    float acc = 0.f;
+    bool vec = group_aligned<SDT, G>(src);
+    if constexpr (STORE) vec = vec && group_aligned<DDT, G>(dst);
+
+    if (vec) {
+      const int64_t full = len / kTileElems * kTileElems;
+      for (int64_t t0 = 0; t0 < full; t0 += kTileElems) {
+        float x[U][G];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          GroupIO<SDT, G>::load(src, t0 + u * (kThreads * G) + threadIdx.x * G, x[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+          for (int k = 0; k < G; ++k) {
+            float y = __fmul_rn(x[u][k], scale);
+            if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+            x[u][k] = y;
+          }
+          if constexpr (STORE)
+            GroupIO<DDT, G>::store(dst, t0 + u * (kThreads * G) + threadIdx.x * G, x[u]);
+        }
+      }
+      // ragged end of the chunk: whole groups, then single elements
+      const int64_t groups_end = len / G * G;
+      for (int64_t i = full + (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
+        float x[G];
+        GroupIO<SDT, G>::load(src, i, x);
+#pragma unroll
+        for (int k = 0; k < G; ++k) {
+          float y = __fmul_rn(x[k], scale);
+          if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+          x[k] = y;
+        }
+        if constexpr (STORE) GroupIO<DDT, G>::store(dst, i, x);
+      }
+      for (int64_t i = groups_end + threadIdx.x; i < len; i += kThreads) {
+        float y = __fmul_rn(load1<SDT>(src, i), scale);
+        if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+        if constexpr (STORE) store1<DDT>(dst, i, y);
+      }
+    } else {
+      // a segment whose base is not 16-byte aligned (odd element offset inside a bucket)
+      for (int64_t i = threadIdx.x; i < len; i += kThreads) {
+        float y = __fmul_rn(load1<SDT>(src, i), scale);
+        if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+        if constexpr (STORE) store1<DDT>(dst, i, y);
+      }
+    }
+
+    if constexpr (NORM) {
+      const float total = block_sum(acc, red);
+      if (threadIdx.x == 0) chunk_partials[c] = total;
+    }
+  }
+
+  if constexpr (NORM) finish_sumsq(tab, chunk_base, chunk_partials, sumsq_out, total_chunks, ticket);
+}
+
+template <int SDT, int DDT, int SRC, int DST, bool STORE, bool NORM, bool DEVSCALE>
+static int launch_stream(const ddpb200_seg* table, int table_loc, int64_t n, int64_t total_chunks,
+                         int64_t chunk_elems, float scale, const float* scale_ptr, float* sumsq_out,
+                         float* chunk_partials, uint32_t* ticket, cudaStream_t st) {
+  if (!valid_chunking(n, total_chunks, chunk_elems) || (n > 0 && !table)) return DDPB200_E_INVALID;
+  if (NORM && n > 0 && (!sumsq_out || !ticket || (total_chunks > 0 && !chunk_partials)))
+    return DDPB200_E_INVALID;
+  if (n == 0) return 0;
+  return for_each_table_slice(table, table_loc == DDPB200_TABLE_DEVICE, n, total_chunks,
+    [&](auto& tab, int64_t chunks, int64_t seg_off, int64_t chunk_off) -> int {
+      using Tab = std::remove_reference_t<decltype(tab)>;
+      int err = 0;
+      int grid = persistent_grid(chunks, &err);
+      if (err) return err;
+      if (grid == 0) {
+        if (!NORM) return 0;
+        grid = 1;  // all segments empty: still write zeros to sumsq_out
+      }
+      stream_kernel<Tab, SDT, DDT, SRC, DST, STORE, NORM, DEVSCALE><<<grid, kThreads, 0, st>>>(
+          tab, chunks, chunk_elems, scale, scale_ptr, NORM ? sumsq_out + seg_off : nullptr,
+          NORM ? chunk_partials + chunk_off : nullptr, ticket);
+      return (int)cudaGetLastError();
+    });
+}
+
+}  // namespace ddpb200
+
+using namespace ddpb200;
+
+extern "C" DDPB200_API int ddpb200_pack_scale_cast(const ddpb200_seg* table, int32_t table_loc, int64_t n,
+                                       int64_t total_chunks, int64_t chunk_elems,
+                                       int32_t src_dtype, int32_t dst_dtype, float scale,
+                                       float* sumsq_out, float* chunk_partials, uint32_t* ticket,
+                                       void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define DDPB200_PACK_CASE(S, D)                                                                  \
+  if (src_dtype == S && dst_dtype == D) {                                                        \
+    return sumsq_out                                                                             \
+      ? launch_stream<S, D, 0, 1, true, true, false>(table, table_loc, n, total_chunks,          \
+            chunk_elems, scale, nullptr, sumsq_out, chunk_partials, ticket, st)                  \
+      : launch_stream<S, D, 0, 1, true, false, false>(table, table_loc, n, total_chunks,         \
+            chunk_elems, scale, nullptr, nullptr, nullptr, nullptr, st);                         \
+  }
+  DDPB200_PACK_CASE(DDPB200_F32, DDPB200_F32)
+  DDPB200_PACK_CASE(DDPB200_BF16, DDPB200_BF16)
+  DDPB200_PACK_CASE(DDPB200_F32, DDPB200_BF16)
+  DDPB200_PACK_CASE(DDPB200_BF16, DDPB200_F32)
+#undef DDPB200_PACK_CASE
+  return DDPB200_E_UNSUPPORTED;
+}
+
+extern "C" DDPB200_API int ddpb200_l2norm_sumsq(const ddpb200_seg* table, int32_t table_loc, int64_t n,
+                                    int64_t total_chunks, int64_t chunk_elems, int32_t dtype,
+                                    float* sumsq_out, float* chunk_partials, uint32_t* ticket,
+                                    void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DDPB200_F32)
+    return launch_stream<DDPB200_F32, DDPB200_F32, 1, 1, false, true, false>(
+        table, table_loc, n, total_chunks, chunk_elems, 1.0f, nullptr, sumsq_out, chunk_partials, ticket, st);
+  if (dtype == DDPB200_BF16)
+    return launch_stream<DDPB200_BF16, DDPB200_BF16, 1, 1, false, true, false>(
+        table, table_loc, n, total_chunks, chunk_elems, 1.0f, nullptr, sumsq_out, chunk_partials, ticket, st);
+  return DDPB200_E_UNSUPPORTED;
+}
+
+extern "C" DDPB200_API int ddpb200_scale_by_device_scalar(const ddpb200_seg* table, int32_t table_loc,
+                                              int64_t n, int64_t total_chunks,
+                                              int64_t chunk_elems, int32_t dtype,
+                                              const float* coef, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!coef) return DDPB200_E_INVALID;
+  if (dtype == DDPB200_F32)
+    return launch_stream<DDPB200_F32, DDPB200_F32, 1, 1, true, false, true>(
+        table, table_loc, n, total_chunks, chunk_elems, 1.0f, coef, nullptr, nullptr, nullptr, st);
+  if (dtype == DDPB200_BF16)
+    return launch_stream<DDPB200_BF16, DDPB200_BF16, 1, 1, true, false, true>(
+        table, table_loc, n, total_chunks, chunk_elems, 1.0f, coef, nullptr, nullptr, nullptr, st);
+  return DDPB200_E_UNSUPPORTED;
+}
+
+// ---- total norm + clip coefficient ----------------------------------------------------
+namespace ddpb200 {
+
+__global__ void __launch_bounds__(kThreads, 1)
+norm_finalize_kernel(const float* __restrict__ sumsq, int64_t n, int mode, float max_norm,
+                     float* __restrict__ out) {
+  __shared__ double red[kThreads / 32];
+  double acc = 0.0;
+  for (int64_t i = threadIdx.x; i < n; i += kThreads) {
+    float ss = sumsq[i];
+    if (mode == DDPB200_NORM_TORCH_BF16) {
+      // torch._foreach_norm returns each tensor's norm in the grad dtype; vector_norm then
+      // squares those rounded values in fp32 (clip_grad.py:96,106-108)
+      const float nt = round_through_bf16(__fsqrt_rn(ss));
+      ss = __fmul_rn(nt, nt);
+    }
+    acc += (double)ss;
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < kThreads / 32; ++w) t += red[w];
+    float total = __fsqrt_rn((float)t);
+    float coef;
+    if (mode == DDPB200_NORM_TORCH_BF16) {
+      total = round_through_bf16(total);
+      const float d = round_through_bf16(__fadd_rn(total, 1e-6f));   // total_norm + 1e-6
+      coef = round_through_bf16(__fdiv_rn(max_norm, d));              // max_norm / (...)
+    } else {
+      coef = __fdiv_rn(max_norm, __fadd_rn(total, 1e-6f));
+    }
+    coef = (coef != coef) ? coef : fminf(coef, 1.0f);                 // clamp(max=1.0) keeps NaN
+    out[0] = total;
+    out[1] = coef;
+  }
+}
+
+}  // namespace ddpb200
+
+extern "C" DDPB200_API int ddpb200_l2norm_finalize(const float* sumsq, int64_t n, int32_t mode,
+                                       float max_norm, float* out, void* stream) {
+  if (n < 0 || !out || (n > 0 && !sumsq)) return DDPB200_E_INVALID;
+  if (mode != DDPB200_NORM_EXACT_F32 && mode != DDPB200_NORM_TORCH_BF16) return DDPB200_E_INVALID;
+  norm_finalize_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(sumsq, n, mode, max_norm, out);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,519 @@
+"""DistributedDataParallel with the gradient-sync half rebuilt for B200.
+
+Drop-in for ``torch.nn.parallel.DistributedDataParallel`` on the data-parallel path
+(TORCH/nn/parallel/distributed.py:655-972 ctor, :1693-1701 forward, :1987-2066 comm hooks) and
+for the C++ Reducer behind it (TORCH/include/torch/csrc/distributed/c10d/reducer.hpp): same
+constructor keywords, same bucket layouts (bit-exact: one bucket in registration order for the
+first iteration, then rebuilt in rank 0's gradient-ready order with [first_cap, cap] limits),
+same averaging arithmetic (round(fp32(g) * float(1/world_size)) then SUM), same comm-hook
+protocol, ``no_sync()``, and ``module.``-prefixed state_dict.
+
+What is different is how the bytes move:
+  * one pack launch per BUCKET (flatten + scale + cast, 16-byte vectors) instead of one
+    elementwise launch per parameter (reducer.hpp:276);
+  * the bucket allreduce runs on a dedicated side stream as soon as the bucket is packed, and the
+    per-tensor sum of squares needed by clip_grad_norm_ is taken on that stream right behind the
+    allreduce while backward is still running — so the global-norm barrier costs one tiny
+    finalize kernel after backward (``ddp.clip_grad_norm_``);
+  * with ``gradient_as_bucket_view=True`` the fused clip+AdamW kernel reads gradients straight
+    from the buckets: there is no unpack pass at all.
+
+One process drives one GPU. ``find_unused_parameters=True``, sparse gradients, multi-device
+modules and ``join()`` are outside the path this package covers and raise.
+"""
+from __future__ import annotations
+
+import sys
+import weakref
+from contextlib import contextmanager
+from typing import Callable, List, Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from . import bucketing
+from .kernels import default_kernels
+
+
+class GradBucket:
+    """What a communication hook receives: mirrors ``dist.GradBucket`` (index, buffer, gradients,
+    parameters, is_last, set_buffer) — TORCH/nn/parallel/distributed.py:1987-2035."""
+
+    def __init__(self, index: int, buffer: torch.Tensor, gradients: List[torch.Tensor],
+                 parameters: List[torch.Tensor], is_last: bool):
+        self._index, self._buffer, self._gradients = index, buffer, gradients
+        self._parameters, self._is_last = parameters, is_last
+
+    def index(self) -> int:
+        return self._index
+
+    def buffer(self) -> torch.Tensor:
+        return self._buffer
+
+    def gradients(self) -> List[torch.Tensor]:
+        return self._gradients
+
+    def parameters(self) -> List[torch.Tensor]:
+        return self._parameters
+
+    def is_last(self) -> bool:
+        return self._is_last
+
+    def set_buffer(self, tensor: torch.Tensor) -> None:
+        self._buffer = tensor
+
+
+class _Bucket:
+    __slots__ = ("index", "spec", "buffer", "views", "first", "pending", "future", "work", "dtype")
+
+    def __init__(self, index, spec, buffer, views, first):
+        self.index, self.spec, self.buffer, self.views, self.first = index, spec, buffer, views, first
+        self.pending = len(spec.indices)
+        self.future = None
+        self.work = None
+        self.dtype = buffer.dtype
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
+                 broadcast_buffers: bool = True, init_sync: bool = True, process_group=None,
+                 bucket_cap_mb: Optional[float] = None, find_unused_parameters: bool = False,
+                 check_reduction: bool = False, gradient_as_bucket_view: bool = False,
+                 static_graph: bool = False, delay_all_reduce_named_params=None,
+                 param_to_hook_all_reduce=None, mixed_precision=None, device_mesh=None,
+                 skip_all_reduce_unused_params: bool = False, *, kernels=None):
+        super().__init__()
+        if find_unused_parameters:
+            raise NotImplementedError("ddp_b200: find_unused_parameters=True is outside the hot path covered")
+        if delay_all_reduce_named_params or mixed_precision is not None or device_mesh is not None:
+            raise NotImplementedError("ddp_b200: delay_all_reduce / mixed_precision / device_mesh are not covered")
+        self.module = module
+        self.dim = dim
+        self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = False
+        self.static_graph = static_graph
+        self.gradient_as_bucket_view = gradient_as_bucket_view
+        self.require_backward_grad_sync = True
+        self.process_group = process_group if process_group is not None else dist.group.WORLD
+        self.world_size = dist.get_world_size(self.process_group)
+        self.rank = dist.get_rank(self.process_group)
+        self.parameters_to_ignore = set(getattr(module, "_ddp_params_and_buffers_to_ignore", []))
+
+        # reduction bucket size (distributed.py:831-853)
+        if bucket_cap_mb is None:
+            bucket_cap_mb, self.bucket_bytes_cap_default = 25, True
+        else:
+            self.bucket_bytes_cap_default = False
+        self.bucket_bytes_cap = int(bucket_cap_mb * 1024 * 1024)
+        self.broadcast_bucket_size = 250 * 1024 * 1024
+
+        self._params: List[nn.Parameter] = self._build_params_for_reducer()
+        if not self._params:
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any "
+                               "parameter that requires a gradient.")
+        devs = {p.device for p in self._params}
+        if len(devs) != 1:
+            raise NotImplementedError("ddp_b200: one process drives one device; parameters span several")
+        self.device = devs.pop()
+        self._cuda = self.device.type == "cuda"
+        if device_ids is not None and self._cuda and len(device_ids) == 1:
+            d = device_ids[0]
+            d = d.index if isinstance(d, torch.device) else int(d)
+            if d != self.device.index:
+                raise ValueError(f"device_ids {device_ids} does not match the module's device {self.device}")
+        self.device_ids = device_ids
+        self.output_device = output_device
+        self._kernels = kernels if kernels is not None else default_kernels()
+        if any(p.is_sparse for p in self._params):
+            raise NotImplementedError("ddp_b200: sparse parameters are not covered")
+
+        if init_sync:
+            self._verify_param_shapes()
+            self._sync_module_states()
+
+        self._comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self._cuda else None
+        self._comm_hook: Optional[Callable] = None
+        self._comm_hook_state = None
+        self._hook_handles = []
+        self._has_rebuilt = False
+        self._ready_order: List[int] = []
+        self._expect_hooks = False
+        self._callback_queued = False
+        self._next_bucket = 0
+        self._sumsq_valid = False
+        self._stats = {"iterations": 0, "pack_launches": 0, "allreduces": 0, "norm_launches": 0,
+                       "unpack_launches": 0, "rebuilt_bucket_sizes": []}
+
+        limits = bucketing.initial_bucket_limits(False, static_graph, self.bucket_bytes_cap,
+                                                 self.bucket_bytes_cap_default)
+        idx, lim = bucketing.compute_bucket_assignment_by_size(self._params, limits)
+        # reversed: approximate the order in which gradients become ready (distributed.py:1254-1258)
+        self._build_buckets(list(reversed(idx)), list(reversed(lim)))
+
+        ref = weakref.ref(self)
+        for i, p in enumerate(self._params):
+            def hook(param, _i=i, _ref=ref):
+                me = _ref()
+                if me is not None:
+                    me._on_grad_ready(_i, True)
+            self._hook_handles.append(p.register_post_accumulate_grad_hook(hook))
+
+    # ---- construction helpers --------------------------------------------------------------
+    def _build_params_for_reducer(self) -> List[nn.Parameter]:
+        """Parameters in registration order, shared ones once (distributed.py:1338-1382)."""
+        seen, out = set(), []
+        for mname, mod in self.module.named_modules():
+            for pname, p in mod.named_parameters(recurse=False):
+                if not p.requires_grad or f"{mname}.{pname}" in self.parameters_to_ignore:
+                    continue
+                if isinstance(mod, (nn.Embedding, nn.EmbeddingBag)) and mod.sparse:
+                    raise NotImplementedError("ddp_b200: sparse-gradient embeddings are not covered")
+                if p not in seen:
+                    seen.add(p)
+                    out.append(p)
+        return out
+
+    def _verify_param_shapes(self) -> None:
+        """All ranks must hold the same parameter list (_verify_param_shape_across_processes,
+        distributed.py:881)."""
+        if self.world_size == 1:
+            return
+        sizes = torch.tensor([len(self._params)] + [p.numel() for p in self._params], dtype=torch.int64,
+                             device=self.device)
+        ref = sizes.clone()
+        dist.broadcast(ref, src=dist.get_global_rank(self.process_group, 0), group=self.process_group)
+        if not torch.equal(ref, sizes):
+            raise RuntimeError("DDP expects same model across all ranks, but parameter sizes differ from rank 0")
+
+    def _sync_module_states(self) -> None:
+        """Broadcast parameters and buffers from rank 0 in flat chunks of at most 250 MiB
+        (_sync_module_states, distributed.py:883-890)."""
+        if self.world_size == 1:
+            return
+        tensors = [p.detach() for n, p in self.module.named_parameters() if n not in self.parameters_to_ignore]
+        if self.broadcast_buffers:
+            tensors += [b.detach() for n, b in self.module.named_buffers() if n not in self.parameters_to_ignore]
+        self._broadcast_coalesced(tensors)
+
+    def _broadcast_coalesced(self, tensors: List[torch.Tensor]) -> None:
+        src = dist.get_global_rank(self.process_group, 0)
+        by_dtype = {}
+        for t in tensors:
+            by_dtype.setdefault((t.dtype, t.device), []).append(t)
+        for (_, _), ts in by_dtype.items():
+            chunk, size = [], 0
+            for t in ts + [None]:
+                if t is not None and (size == 0 or size + t.numel() * t.element_size() <= self.broadcast_bucket_size):
+                    chunk.append(t)
+                    size += t.numel() * t.element_size()
+                    continue
+                if chunk:
+                    flat = torch.cat([c.reshape(-1) for c in chunk])
+                    dist.broadcast(flat, src=src, group=self.process_group)
+                    off = 0
+                    for c in chunk:
+                        c.copy_(flat[off:off + c.numel()].view_as(c))
+                        off += c.numel()
+                chunk, size = ([t], t.numel() * t.element_size()) if t is not None else ([], 0)
+
+    def _build_buckets(self, bucket_indices: List[List[int]], limits: List[int]) -> None:
+        numels = [p.numel() for p in self._params]
+        specs = bucketing.layout_buckets(numels, bucket_indices, limits)
+        self._buckets: List[_Bucket] = []
+        self._order: List[int] = []
+        first = 0
+        for b, spec in enumerate(specs):
+            dt = self._params[spec.indices[0]].dtype
+            buf = torch.zeros(spec.numel, dtype=dt, device=self.device)
+            views = [buf[o:o + numels[i]].view_as(self._params[i]) for i, o in zip(spec.indices, spec.offsets)]
+            self._buckets.append(_Bucket(b, spec, buf, views, first))
+            self._order.extend(spec.indices)
+            first += len(spec.indices)
+        n = len(self._order)
+        self._slot_of = {pi: s for s, pi in enumerate(self._order)}
+        self._bucket_of = {pi: bk for bk in self._buckets for pi in bk.spec.indices}
+        all_views = [v for bk in self._buckets for v in bk.views]
+        onum = [numels[i] for i in self._order]
+        k = self._kernels
+        # pack: ptr[0] = this step's grad tensor (changes every step -> host table), ptr[1] = bucket view
+        self._pack_table = k.table([None, all_views, None, None], onum)
+        # unpack: ptr[0] = bucket view, ptr[1] = grad tensor
+        self._unpack_table = k.table([all_views, None, None, None], onum, chunk_elems=self._pack_table.chunk_elems)
+        # norm / in-place clip over the bucket views: static pointers -> device-resident table
+        self._view_table = k.table([None, all_views, None, None], onum, chunk_elems=self._pack_table.chunk_elems,
+                                   device=self.device if self._cuda else None)
+        self._sumsq = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self._norm_out = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self._sumsq_valid = False
+        self._next_bucket = 0
+
+    # ---- public surface shared with torch's DDP -------------------------------------------------
+    def forward(self, *inputs, **kwargs):
+        if torch.is_grad_enabled() and self.require_backward_grad_sync:
+            self._rebuild_buckets()
+            self._prepare_for_backward()
+        if self.broadcast_buffers and self.world_size > 1 and self.require_backward_grad_sync:
+            bufs = [b for _, b in self.module.named_buffers()]
+            if bufs:
+                with torch.no_grad():
+                    self._broadcast_coalesced(bufs)     # _sync_buffers, distributed.py:1553-1600
+        if self.device_ids is not None:
+            inputs, kwargs = self._to_device(inputs), self._to_device(kwargs)   # _pre_forward, distributed.py:1602-1622
+        return self.module(*inputs, **kwargs)
+
+    def _to_device(self, obj):
+        if isinstance(obj, torch.Tensor):
+            return obj if obj.device == self.device else obj.to(self.device, non_blocking=True)
+        if isinstance(obj, tuple):
+            return tuple(self._to_device(o) for o in obj)
+        if isinstance(obj, list):
+            return [self._to_device(o) for o in obj]
+        if isinstance(obj, dict):
+            return {k: self._to_device(v) for k, v in obj.items()}
+        return obj
+
+    @contextmanager
+    def no_sync(self):
+        """Skip gradient synchronisation inside the context; gradients accumulate locally and are
+        reduced by the first backward after it (distributed.py:1472-1498)."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def register_comm_hook(self, state, hook: Callable) -> None:
+        """hook(state, bucket) -> Future[Tensor]; buckets arrive NOT pre-divided
+        (distributed.py:1987-2035). One registration only, before the first backward."""
+        if self._comm_hook is not None:
+            raise RuntimeError("register_comm_hook or register_builtin_comm_hook can only be called once.")
+        if not callable(hook):
+            raise TypeError("Communication hook must be callable.")
+        self._comm_hook, self._comm_hook_state = hook, state
+
+    def _get_ddp_logging_data(self) -> dict:
+        d = dict(self._stats)
+        d["world_size"] = self.world_size
+        d["bucket_sizes"] = [bk.buffer.numel() * bk.buffer.element_size() for bk in self._buckets]
+        d["has_rebuilt_buckets"] = self._has_rebuilt
+        d["gradient_as_bucket_view"] = self.gradient_as_bucket_view
+        d["backend_name"] = dist.get_backend(self.process_group)
+        d["kernel_backend"] = getattr(self._kernels, "name", type(self._kernels).__name__)
+        return d
+
+    def bucket_layout(self) -> List[dict]:
+        """Current buckets: parameter indices, element offsets and lengths (for parity checks)."""
+        return [dict(index=bk.index, parameters=list(bk.spec.indices), offsets=list(bk.spec.offsets),
+                     numel=bk.spec.numel, size_limit=bk.spec.size_limit) for bk in self._buckets]
+
+    # ---- reducer --------------------------------------------------------------------------------
+    def _prepare_for_backward(self) -> None:
+        self._expect_hooks = True
+        self._next_bucket = 0
+        self._callback_queued = False
+        self._sumsq_valid = False
+        for bk in self._buckets:
+            bk.pending = len(bk.spec.indices)
+            bk.future = bk.work = None
+
+    def _rebuild_buckets(self) -> bool:
+        """Once, after the first synchronised backward: re-bucket in the order gradients became
+        ready on rank 0, with limits [first_bucket_bytes_cap, bucket_bytes_cap]
+        (Reducer::rebuild_buckets, reducer.hpp:146-151,299-301; triggered distributed.py:1584)."""
+        if self._has_rebuilt or not self._ready_order:
+            return False
+        n = len(self._params)
+        order = torch.tensor(self._ready_order if len(self._ready_order) == n else list(range(n)),
+                             dtype=torch.int64, device=self.device)
+        if self.world_size > 1:
+            dist.broadcast(order, src=dist.get_global_rank(self.process_group, 0), group=self.process_group)
+        order = [int(x) for x in order.tolist()]
+        limits = bucketing.rebuild_bucket_limits(self.bucket_bytes_cap, self.bucket_bytes_cap_default)
+        idx, lim = bucketing.compute_bucket_assignment_by_size([self._params[i] for i in order], limits,
+                                                               None, order)
+        if self.gradient_as_bucket_view:
+            for p in self._params:          # grads alias the old buckets: detach before freeing them
+                if p.grad is not None:
+                    p.grad = p.grad.clone()
+        if self._cuda:
+            torch.cuda.current_stream().wait_stream(self._comm_stream)
+        self._build_buckets(idx, lim)
+        self._has_rebuilt = True
+        self._ready_order = []
+        self._stats["rebuilt_bucket_sizes"] = [bk.buffer.numel() * bk.buffer.element_size() for bk in self._buckets]
+        return True
+
+    def _on_grad_ready(self, idx: int, from_autograd: bool) -> None:
+        """Per-parameter hook (Reducer::autograd_hook -> mark_variable_ready, reducer.hpp:74,276):
+        runs on the autograd thread, with that thread's current stream = the compute stream."""
+        if not self._expect_hooks or not self.require_backward_grad_sync:
+            return
+        if from_autograd and not self._callback_queued:
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+        if not self._has_rebuilt:
+            self._ready_order.append(idx)
+        bk = self._bucket_of[idx]
+        bk.pending -= 1
+        if bk.pending < 0:
+            raise RuntimeError("ddp_b200: a parameter was marked ready twice in one backward "
+                               "(shared across multiple forward passes needs static_graph / no_sync)")
+        # buckets are reduced strictly in sequence so every rank issues the same collectives in
+        # the same order (mark_bucket_ready, reducer.hpp:282)
+        while self._next_bucket < len(self._buckets) and self._buckets[self._next_bucket].pending == 0:
+            self._launch_bucket(self._buckets[self._next_bucket])
+            self._next_bucket += 1
+
+    def _launch_bucket(self, bk: _Bucket) -> None:
+        k = self._kernels
+        n = len(bk.spec.indices)
+        grads = []
+        for pi, view in zip(bk.spec.indices, bk.views):
+            g = self._params[pi].grad
+            if g is None:
+                raise RuntimeError("ddp_b200: gradient missing for a parameter marked ready")
+            if not g.is_contiguous():
+                g = g.contiguous()
+                self._params[pi].grad = g
+            grads.append(g)
+        gdt = grads[0].dtype
+        if any(g.dtype != gdt for g in grads):
+            raise RuntimeError("ddp_b200: gradients of one bucket must share a dtype")
+        self._pack_table.host["ptr"][bk.first:bk.first + n, 0] = np.fromiter(
+            (g.data_ptr() for g in grads), dtype=np.uint64, count=n)
+        hooked = self._comm_hook is not None
+        # no hook: pre-divide, then SUM (div_factor_, reducer.hpp:497-500). With a hook the hook divides.
+        scale = 1.0 if hooked else float(np.float32(1.0 / self.world_size))
+        local_only = self.world_size == 1 and not hooked
+        sumsq_slice = self._sumsq[bk.first:bk.first + n]
+        if local_only and not self.gradient_as_bucket_view:
+            # world_size 1, grads stay where autograd put them: nothing to exchange or copy, only the
+            # norm pass is left (ptr[1] = grad)
+            self._unpack_table.host["ptr"][bk.first:bk.first + n, 1] = self._pack_table.host["ptr"][bk.first:bk.first + n, 0]
+            k.sumsq(self._unpack_table, gdt, sumsq_slice, first=bk.first, count=n, prefer_device=False)
+            self._stats["norm_launches"] += 1
+            return
+        # world_size 1 with bucket views: the norm rides on the pack pass
+        k.pack(self._pack_table, gdt, bk.dtype, scale, first=bk.first, count=n,
+               sumsq_out=sumsq_slice if local_only else None, prefer_device=False)
+        self._stats["pack_launches"] += 1
+        if local_only:
+            return
+        if hooked:
+            gb = GradBucket(bk.index, bk.buffer, list(bk.views), [self._params[i] for i in bk.spec.indices],
+                            bk.index == len(self._buckets) - 1)
+            bk.future = self._comm_hook(self._comm_hook_state, gb)
+            self._stats["allreduces"] += 1
+            return
+        if self._cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            with torch.cuda.stream(self._comm_stream):
+                self._comm_stream.wait_event(ev)
+                work = dist.all_reduce(bk.buffer, group=self.process_group, async_op=True)
+                work.wait()          # stream-level: the side stream waits for NCCL's stream
+                self._after_reduce(bk, grads)
+        else:
+            dist.all_reduce(bk.buffer, group=self.process_group)
+            self._after_reduce(bk, grads)
+        self._stats["allreduces"] += 1
+
+    def _after_reduce(self, bk: _Bucket, grads: List[torch.Tensor]) -> None:
+        """Behind the allreduce, on the same stream: per-tensor sum of squares of the averaged
+        gradients, and (unless grads are bucket views) the copy back into p.grad
+        (finalize_bucket_dense / copy_bucket_to_grad, reducer.hpp:328-334)."""
+        k = self._kernels
+        n = len(bk.spec.indices)
+        if self.gradient_as_bucket_view:
+            k.sumsq(self._view_table, bk.dtype, self._sumsq[bk.first:bk.first + n], first=bk.first, count=n)
+            self._stats["norm_launches"] += 1
+        else:
+            self._unpack_table.host["ptr"][bk.first:bk.first + n, 1] = np.fromiter(
+                (g.data_ptr() for g in grads), dtype=np.uint64, count=n)
+            # unpack and norm in one pass over the bucket
+            k.pack(self._unpack_table, bk.dtype, grads[0].dtype, 1.0, first=bk.first, count=n,
+                   sumsq_out=self._sumsq[bk.first:bk.first + n], prefer_device=False)
+            self._stats["unpack_launches"] += 1
+
+    def _finalize_backward(self) -> None:
+        """End of backward (Reducer::finalize_backward, reducer.hpp:286)."""
+        if not self._expect_hooks:
+            return
+        self._expect_hooks = False
+        self._callback_queued = False
+        if self._next_bucket != len(self._buckets):
+            missing = [pi for bk in self._buckets[self._next_bucket:] for pi in bk.spec.indices
+                       if self._params[pi].grad is None]
+            raise RuntimeError(
+                "Expected to have finished reduction in the prior iteration before starting a new one: "
+                f"{len(missing)} parameter(s) received no gradient (indices {missing[:8]}...). "
+                "ddp_b200 does not cover find_unused_parameters=True.")
+        if self._comm_hook is not None:
+            for bk in self._buckets:
+                result = bk.future.wait()
+                if isinstance(result, (list, tuple)):
+                    result = result[0]
+                if result.data_ptr() != bk.buffer.data_ptr():
+                    bk.buffer.copy_(result.view_as(bk.buffer))      # populate_bucket_views_out, reducer.hpp:323-326
+                self._after_reduce(bk, [self._params[pi].grad for pi in bk.spec.indices])
+        elif self._cuda and self.world_size > 1:
+            torch.cuda.current_stream().wait_stream(self._comm_stream)
+        if self.gradient_as_bucket_view:
+            for bk in self._buckets:
+                for pi, view in zip(bk.spec.indices, bk.views):
+                    p = self._params[pi]
+                    if p.grad is None or p.grad.data_ptr() != view.data_ptr():
+                        p.grad = view
+        self._sumsq_valid = True
+        self._stats["iterations"] += 1
+
+    # ---- beyond torch: feed gradients by hand, and the overlapped global norm ---------------------
+    def reduce_gradients(self, grads: Optional[List[torch.Tensor]] = None,
+                         order: Optional[List[int]] = None) -> None:
+        """Run one gradient synchronisation outside autograd: optionally install ``grads`` (one per
+        parameter, registration order) as ``p.grad``, then mark parameters ready in ``order``
+        (default: the current bucket order) and finalize. Same scheduler as a real backward."""
+        self._rebuild_buckets()
+        self._prepare_for_backward()
+        if grads is not None:
+            for p, g in zip(self._params, grads):
+                p.grad = g
+        for pi in (order if order is not None else self._order):
+            self._on_grad_ready(pi, False)
+        self._finalize_backward()
+
+    def clip_grad_norm_(self, max_norm: float, norm_type: float = 2.0, error_if_nonfinite: bool = False,
+                        *, fused_optimizer=None, torch_rounding: bool = True) -> torch.Tensor:
+        """``torch.nn.utils.clip_grad_norm_`` over this module's parameters
+        (TORCH/nn/utils/clip_grad.py:186-233) using the sums of squares that were taken behind each
+        bucket's allreduce during backward: what is left is one tiny finalize kernel, plus the
+        in-place scale unless ``fused_optimizer`` takes the coefficient into its update kernel."""
+        if float(norm_type) != 2.0:
+            raise NotImplementedError("ddp_b200: L2 norm only")
+        if not self._sumsq_valid:
+            raise RuntimeError("ddp.clip_grad_norm_ needs a completed synchronised backward; "
+                               "use ddp_b200.clip_grad_norm_(parameters, ...) otherwise")
+        k = self._kernels
+        all_bf16 = all(bk.dtype == torch.bfloat16 for bk in self._buckets)
+        out = k.norm_finalize(self._sumsq, float(max_norm), torch_bf16=(torch_rounding and all_bf16),
+                              out=self._norm_out)
+        if error_if_nonfinite and not bool(torch.isfinite(out[0])):
+            raise RuntimeError("The total norm for gradients from `parameters` is non-finite, so it cannot be clipped.")
+        coef = out[1:2]
+        if fused_optimizer is not None:
+            fused_optimizer.set_clip_coef(coef)
+        elif self.gradient_as_bucket_view:
+            for bk in self._buckets:
+                k.scale_by(self._view_table, bk.dtype, coef, first=bk.first, count=len(bk.spec.indices))
+        else:
+            by_dt = {}
+            for p in self._params:
+                by_dt.setdefault(p.grad.dtype, []).append(p.grad)
+            for dt, gl in by_dt.items():
+                tab = k.table([None, gl, None, None], [g.numel() for g in gl])
+                k.scale_by(tab, dt, coef, prefer_device=False)
+        self._sumsq_valid = fused_optimizer is not None   # grads changed in place otherwise
+        return out[0].to(self._buckets[0].dtype)

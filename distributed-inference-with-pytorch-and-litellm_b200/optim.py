@@ -1,0 +1,140 @@
+"""AdamW with the update done by ONE fused sm_100a kernel launch per (dtype) group.
+
+Drop-in for ``torch.optim.AdamW`` (TORCH/optim/adamw.py:20-49; step logic TORCH/optim/adam.py:
+215-272): same constructor arguments, ``step`` / ``zero_grad`` / ``state_dict`` /
+``load_state_dict`` and the same per-parameter state (``step``, ``exp_avg``, ``exp_avg_sq``).
+The element arithmetic follows torch's fused functor (TORCH/include/ATen/native/cuda/
+fused_adam_utils.cuh:41-93); see csrc/adamw.cu.
+
+Beyond torch: the gradient-clipping multiply of ``clip_grad_norm_`` can be folded into the same
+pass (``clip_grad_norm_(..., fused_optimizer=opt)`` or ``step(clip_coef=...)``), which removes a
+read+write sweep over all gradients.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+from torch.optim.optimizer import Optimizer
+
+from .kernels import SegTable, default_kernels
+
+
+class AdamW(Optimizer):
+    # GradScaler hands grad_scale / found_inf to optimizers that declare this (TORCH/amp/grad_scaler.py)
+    _step_supports_amp_scaling = True
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, amsgrad=False,
+                 *, maximize: bool = False, foreach: Optional[bool] = None, capturable: bool = False,
+                 differentiable: bool = False, fused: Optional[bool] = None,
+                 state_dtype: Optional[torch.dtype] = None, kernels=None):
+        if isinstance(lr, torch.Tensor) and lr.numel() != 1:
+            raise ValueError("Tensor lr must be 1-element")
+        if not 0.0 <= (float(lr) if not isinstance(lr, torch.Tensor) else float(lr)):
+            raise ValueError(f"Invalid learning rate: {lr}")
+        if not 0.0 <= eps:
+            raise ValueError(f"Invalid epsilon value: {eps}")
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 0: {betas[0]}")
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 1: {betas[1]}")
+        if not 0.0 <= weight_decay:
+            raise ValueError(f"Invalid weight_decay value: {weight_decay}")
+        if amsgrad:
+            raise NotImplementedError("ddp_b200.AdamW: amsgrad=True is outside the DDP hot path this package covers")
+        if differentiable:
+            raise NotImplementedError("ddp_b200.AdamW: differentiable=True is not supported by the fused kernel")
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad,
+                        maximize=maximize, foreach=foreach, capturable=capturable,
+                        differentiable=differentiable, fused=fused, decoupled_weight_decay=True)
+        super().__init__(params, defaults)
+        self._kernels = kernels
+        self._state_dtype = state_dtype
+        self._clip_coef: Optional[torch.Tensor] = None
+        self._tables: Dict[Tuple, Tuple[np.ndarray, np.ndarray, SegTable]] = {}
+        self.round_clipped_grad = True   # reproduce torch's rounding of g*coef to the grad dtype
+        self.launches_last_step = 0
+
+    # ---- clip folding -------------------------------------------------------------------------
+    def set_clip_coef(self, coef: Optional[torch.Tensor]) -> None:
+        """Device fp32 scalar to multiply every gradient by inside the next ``step`` (then cleared)."""
+        self._clip_coef = coef
+
+    def _k(self):
+        if self._kernels is None:
+            self._kernels = default_kernels()
+        return self._kernels
+
+    def _init_state(self, p: torch.Tensor) -> dict:
+        st = self.state[p]
+        if len(st) == 0:
+            sdt = self._state_dtype or p.dtype
+            st["step"] = torch.tensor(0.0, dtype=torch.float32)          # adam.py:168-176 (CPU scalar)
+            st["exp_avg"] = torch.zeros_like(p, dtype=sdt, memory_format=torch.preserve_format)     # :178-180
+            st["exp_avg_sq"] = torch.zeros_like(p, dtype=sdt, memory_format=torch.preserve_format)  # :182-184
+        return st
+
+    @torch.no_grad()
+    def step(self, closure=None, *, clip_coef: Optional[torch.Tensor] = None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        if clip_coef is None:
+            clip_coef = self._clip_coef
+        self._clip_coef = None
+        grad_scale = getattr(self, "grad_scale", None)
+        found_inf = getattr(self, "found_inf", None)
+        if found_inf is not None and float(found_inf) == 1.0:
+            return loss  # GradScaler: skip the step, counters untouched (adam.py:869-876)
+        k = self._k()
+        self.launches_last_step = 0
+
+        for gi, group in enumerate(self.param_groups):
+            beta1, beta2 = group["betas"]
+            buckets: Dict[Tuple, List[torch.Tensor]] = {}
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                if p.grad.is_sparse:
+                    raise RuntimeError("AdamW does not support sparse gradients")
+                if not (p.is_contiguous() and p.grad.is_contiguous()):
+                    raise RuntimeError("ddp_b200.AdamW needs contiguous parameters and gradients")
+                st = self._init_state(p)
+                st["step"] += 1
+                key = (p.device, p.dtype, p.grad.dtype, st["exp_avg"].dtype, int(st["step"]))
+                buckets.setdefault(key, []).append(p)
+            for key, plist in buckets.items():
+                device, pdt, gdt, sdt, step = key
+                tab = self._table_for((gi,) + key[:4], plist, device)
+                k.adamw(tab, pdt, gdt, sdt, lr=group["lr"], beta1=beta1, beta2=beta2, eps=group["eps"],
+                        weight_decay=group["weight_decay"], step=step, clip_coef=clip_coef,
+                        grad_scale=grad_scale, found_inf=None, round_clipped=self.round_clipped_grad,
+                        store_grad=grad_scale is not None, maximize=group["maximize"])
+                self.launches_last_step += 1
+        return loss
+
+    def _table_for(self, key, plist: List[torch.Tensor], device) -> SegTable:
+        """Segment table for this group. Parameter / state pointers never move; gradient pointers
+        do when autograd allocates fresh grads each step. A table whose pointers repeat is kept on
+        the device; otherwise it rides in the launch parameters (no copy, no lifetime)."""
+        n = len(plist)
+        pptr = np.fromiter((p.data_ptr() for p in plist), dtype=np.uint64, count=n)
+        gptr = np.fromiter((p.grad.data_ptr() for p in plist), dtype=np.uint64, count=n)
+        ent = self._tables.get(key)
+        if ent is not None and ent[2].n == n and np.array_equal(ent[0], pptr):
+            tab = ent[2]
+            if np.array_equal(ent[1], gptr):
+                if tab.dev is None and device.type == "cuda":
+                    tab.to_device(device)     # second sighting of the same pointers: make it resident
+                return tab
+            tab.host["ptr"][:, 1] = gptr
+            tab.dev = None
+            self._tables[key] = (pptr, gptr, tab)
+            return tab
+        states = [self.state[p] for p in plist]
+        tab = self._k().table([plist, [p.grad for p in plist], [s["exp_avg"] for s in states],
+                               [s["exp_avg_sq"] for s in states]], [p.numel() for p in plist])
+        self._tables[key] = (pptr, gptr, tab)
+        return tab

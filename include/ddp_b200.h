@@ -1,0 +1,178 @@
+/*
+ * ddp_b200.h — C ABI of libddp_b200.so: the B200 (sm_100a) gradient-sync +
+ * clip + AdamW hot path of a DistributedDataParallel fine-tuning step.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers / sizes / scalars and
+ * an explicit cudaStream_t (as void*), allocates nothing and never throws.
+ * Return value: 0 = OK, >0 = cudaError_t, <0 = DDPB200_E_* below.
+ *
+ * "REF/"   = the upstream repo (naman1618/Distributed-Inference-with-PyTorch-and-LiteLLM)
+ * "TORCH/" = torch 2.11.0 site-packages, the un-vendored dependency in which the
+ *            reference's DDP / clip / AdamW arithmetic actually lives
+ *            (REF/requirements.txt:2, REF/README.md:7).
+ *
+ * Vocabulary: a *segment* is one parameter tensor's slot (its grad, its bucket
+ * view, its optimizer state); a *bucket* is a flat buffer holding the grads of
+ * several segments back to back with no padding (TORCH reducer.hpp:347-406);
+ * a *chunk* is the unit of work one CTA streams through registers.
+ */
+#ifndef DDP_B200_H
+#define DDP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDPB200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define DDPB200_API __attribute__((visibility("default")))
+#else
+#define DDPB200_API
+#endif
+
+/* element types of a stream of values in HBM */
+#define DDPB200_F32  0
+#define DDPB200_BF16 1
+
+/* library error codes (negative); positive codes are cudaError_t */
+#define DDPB200_E_INVALID      (-1)  /* null pointer, negative size, bad enum        */
+#define DDPB200_E_UNSUPPORTED  (-2)  /* dtype combination not compiled               */
+#define DDPB200_E_TOO_LARGE    (-3)  /* size beyond a stated limit                   */
+
+/* flags for ddpb200_fused_clip_adamw */
+#define DDPB200_ADAMW_ROUND_CLIPPED_GRAD 1u /* g = round_to_grad_dtype(g*coef) first, as
+                                               TORCH/nn/utils/clip_grad.py:174 leaves it  */
+#define DDPB200_ADAMW_STORE_GRAD         2u /* write the unscaled+clipped grad back        */
+#define DDPB200_ADAMW_MAXIMIZE           4u /* TORCH/optim/adam.py maximize=True           */
+
+/* rounding of the grad-norm scalars (ddpb200_l2norm_finalize) */
+#define DDPB200_NORM_EXACT_F32   0 /* total = sqrt(sum_t sumsq_t), all fp32                 */
+#define DDPB200_NORM_TORCH_BF16  1 /* per-tensor norm, total, total+1e-6, coef and clamp each
+                                      rounded to bf16 as torch does for bf16 grads
+                                      (TORCH/nn/utils/clip_grad.py:96,106-108,165-169)      */
+
+/* where a segment table lives */
+#define DDPB200_TABLE_HOST   0 /* host memory: copied into the launch parameters (no H2D copy, no
+                                  lifetime to manage) — for pointers that change every step    */
+#define DDPB200_TABLE_DEVICE 1 /* device memory: built once, reused every step                  */
+
+/* One segment (parameter tensor) of a multi-tensor launch. 48 bytes, device-resident
+ * table built once by the host and reused every step. What ptr[0..3] mean is stated
+ * per entry point. chunk_begin is the exclusive prefix sum of ceil(numel/chunk_elems). */
+/* A table may be sliced: pass table+first, the slice's n and chunk count; kernels rebase on
+ * the first chunk_begin they see. */
+typedef struct ddpb200_seg {
+  void*   ptr[4];
+  int64_t numel;
+  int64_t chunk_begin;
+} ddpb200_seg;
+
+/* ---- library --------------------------------------------------------------- */
+DDPB200_API int         ddpb200_abi_version(void);
+DDPB200_API const char* ddpb200_error_string(int code);
+/* SM count of the current device (grid sizing); <0 on error. */
+DDPB200_API int         ddpb200_sm_count(void);
+
+/* ---- a-1  bucket planner (host only, integer, bit-exact) -------------------
+ * Replaces dist._compute_bucket_assignment_by_size
+ * (TORCH/include/torch/csrc/distributed/c10d/reducer.hpp:586-598, called at
+ *  TORCH/nn/parallel/distributed.py:1237-1244; BucketAccumulator reducer.hpp:39-43).
+ * Greedy: tensors are appended per (dtype,device) key; a bucket closes when its byte
+ * size reaches the current limit, then that key advances to the next limit; leftovers
+ * are appended; a tensor with expect_sparse[idx]!=0 gets a bucket of its own (limit 0).
+ * tensor_indices==NULL -> indices are 0..n-1 and buckets are finally sorted by their
+ * smallest index; otherwise tensors arrive in grad-ready order and keep it.
+ * Outputs: out_indices[n] (tensor indices, bucket after bucket),
+ *          out_bucket_start[n+1] (bucket b owns out_indices[start[b]..start[b+1])),
+ *          out_bucket_limit[n], *out_n_buckets. */
+DDPB200_API int ddpb200_bucket_assign(const int64_t* numel, const int32_t* elem_size,
+                          const int64_t* key, const uint8_t* expect_sparse,
+                          const int64_t* tensor_indices, int64_t n,
+                          const uint64_t* size_limits, int64_t n_limits,
+                          int64_t* out_indices, int64_t* out_bucket_start,
+                          uint64_t* out_bucket_limit, int64_t* out_n_buckets);
+
+/* Element offsets of each tensor inside its bucket: running sum of numel, no padding
+ * (Bucket.offsets/lengths, TORCH reducer.hpp:372-375). out_offset[i] is for out_indices[i];
+ * out_bucket_numel[b] is the bucket length in elements. */
+DDPB200_API int ddpb200_bucket_layout(const int64_t* numel, const int64_t* indices,
+                          const int64_t* bucket_start, int64_t n_buckets,
+                          int64_t* out_offset, int64_t* out_bucket_numel);
+
+/* ---- segment-table helper (host only) --------------------------------------
+ * Fills seg[i].chunk_begin for a table whose numel fields are set; returns the total
+ * chunk count in *out_total_chunks. chunk_elems must be a positive multiple of 2048. */
+DDPB200_API int ddpb200_plan_chunks(ddpb200_seg* host_table, int64_t n, int64_t chunk_elems,
+                        int64_t* out_total_chunks);
+/* A chunk size that gives every CTA of the persistent grid several chunks. */
+DDPB200_API int64_t ddpb200_suggest_chunk_elems(int64_t total_numel, int32_t sm_count);
+
+/* ---- a-2 / a-4  pack, unpack (+scale, +cast, + optional sum of squares) ------
+ * Replaces the per-parameter `bucket_view = grad * (1/world_size)` of
+ * Reducer::mark_variable_ready_dense (TORCH reducer.hpp:276) and the per-parameter
+ * `grad.copy_(bucket_view)` of finalize_bucket_dense/copy_bucket_to_grad
+ * (reducer.hpp:328-334) by ONE launch per bucket.
+ * ptr[0] = source, ptr[1] = destination. dst[i] = round_dst(fp32(src[i]) * scale);
+ * scale==1.0f is an exact copy/cast. If sumsq_out != NULL, the fp32 sum of squares of the
+ * values as stored in dst is written to sumsq_out[t] per segment (deterministic order;
+ * needs chunk_partials[total_chunks] floats and a zeroed uint32 *ticket, which the kernel
+ * leaves zero again). dst may alias src (in-place scale of a bucket view). */
+DDPB200_API int ddpb200_pack_scale_cast(const ddpb200_seg* table, int32_t table_loc, int64_t n, int64_t total_chunks,
+                            int64_t chunk_elems, int32_t src_dtype, int32_t dst_dtype,
+                            float scale, float* sumsq_out, float* chunk_partials,
+                            uint32_t* ticket, void* stream);
+
+/* ---- a-5  clip_grad_norm_ ----------------------------------------------------
+ * Replaces torch._foreach_norm + stack + vector_norm (TORCH/nn/utils/clip_grad.py:96,
+ * 106-108) with one pass: ptr[1] = grad (read only). Writes per-segment fp32 sums of
+ * squares to sumsq_out[n]. Deterministic (fixed reduction tree; no float atomics). */
+DDPB200_API int ddpb200_l2norm_sumsq(const ddpb200_seg* table, int32_t table_loc, int64_t n, int64_t total_chunks,
+                         int64_t chunk_elems, int32_t dtype, float* sumsq_out,
+                         float* chunk_partials, uint32_t* ticket, void* stream);
+
+/* total norm + clip coefficient, on device, no host sync
+ * (TORCH/nn/utils/clip_grad.py:106-108,165,169). out[0] = total norm (pre-clip),
+ * out[1] = min(max_norm/(total+1e-6), 1). mode = DDPB200_NORM_*. */
+DDPB200_API int ddpb200_l2norm_finalize(const float* sumsq, int64_t n, int32_t mode, float max_norm,
+                            float* out, void* stream);
+
+/* in-place g *= coef[0] for callers that want torch's clip side effect on p.grad
+ * (TORCH/nn/utils/clip_grad.py:174). ptr[1] = grad. */
+DDPB200_API int ddpb200_scale_by_device_scalar(const ddpb200_seg* table, int32_t table_loc, int64_t n,
+                                   int64_t total_chunks, int64_t chunk_elems, int32_t dtype,
+                                   const float* coef, void* stream);
+
+/* ---- a-6  fused unscale + clip + AdamW ---------------------------------------
+ * Replaces torch.optim.AdamW.step (TORCH/optim/adamw.py:20-49, TORCH/optim/adam.py:
+ * 215-272; element math of TORCH/include/ATen/native/cuda/fused_adam_utils.cuh:41-93,
+ * ADAM_MODE::ADAMW, amsgrad=False) and folds in the `g *= clip_coef` pass of
+ * clip_grad.py:174 and GradScaler's unscale. One pass: reads p,g,m,v, writes p,m,v.
+ * ptr[0]=param ptr[1]=grad ptr[2]=exp_avg ptr[3]=exp_avg_sq.
+ *   g  = fp32(grad); if grad_scale: g /= *grad_scale; if clip_coef: g *= *clip_coef
+ *        (rounded to the grad dtype first under DDPB200_ADAMW_ROUND_CLIPPED_GRAD)
+ *   p -= (lr*wd)*p;  m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g
+ *   p -= (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps),  bc = 1 - beta^step (step >= 1)
+ * lr_ptr (device, optional) overrides lr. found_inf (device, optional): if *found_inf==1
+ * the launch is a no-op. clip_coef / grad_scale are device pointers so that no host sync
+ * sits between the norm and the update. */
+DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, int32_t table_loc, int64_t n, int64_t total_chunks,
+                             int64_t chunk_elems, int32_t param_dtype, int32_t grad_dtype,
+                             int32_t state_dtype, double lr, const float* lr_ptr,
+                             double beta1, double beta2, double eps, double weight_decay,
+                             int64_t step, const float* clip_coef, const float* grad_scale,
+                             const float* found_inf, uint32_t flags, void* stream);
+
+/* The two fp32 scalars the kernel derives from `step`: out[0] = 1 - b1^step,
+ * out[1] = sqrt(1 - b2^step), with b = beta rounded to fp32 (as the recurrences use it), the
+ * power taken in double on the host and rounded once
+ * (TORCH/include/ATen/native/cuda/fused_adam_utils.cuh:131-150). */
+DDPB200_API int ddpb200_adamw_bias_corrections(double beta1, double beta2, int64_t step, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDP_B200_H */

@@ -1,0 +1,181 @@
+"""world_size-2 gloo tests of the HOST logic on CPU: bucket scheduling, rebuild in grad-ready order,
+comm hooks, no_sync, gradient_as_bucket_view, the optimizer's table handling. The kernels are
+answered by the test-only oracle backend (tests/oracle_backend.py); what is checked here is the
+plumbing around them, against (a) the golden record of a live stock-torch DDP run on the same
+model and batches and (b) stock torch DDP running side by side in the same processes."""
+import importlib.util
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def _load_golden_module():
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(HERE, "golden", "make_golden.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _setup(rank, ws, port):
+    for p in (ROOT, HERE):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    torch.set_num_threads(1)
+
+
+def _worker_vs_golden(rank, ws, port, gabv):
+    _setup(rank, ws, port)
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    mg = _load_golden_module()
+    z = np.load(os.path.join(HERE, "golden", "ddp_live.npz"))
+    cfg = json.loads(str(z["cfg"]))
+    golden_layout = json.loads(str(z["layout"]))
+    torch.manual_seed(0)
+    net = mg.SmallNet()
+    k = OracleKernels()
+    ddp = ddp_b200.DistributedDataParallel(net, bucket_cap_mb=cfg["bucket_cap_mb"], gradient_as_bucket_view=gabv,
+                                           kernels=k)
+    params = list(net.parameters())
+    opt = ddp_b200.AdamW(params, lr=cfg["lr"], kernels=k)
+    for s in range(cfg["steps"]):
+        ids, tgt = mg.live_batch(s, rank)
+        loss = torch.nn.functional.cross_entropy(ddp(ids).flatten(0, 1), tgt.flatten())
+        # bucket layout in force for this backward == what stock DDP used on that iteration
+        want = sorted([e for e in golden_layout if e[0] == s], key=lambda e: e[1])
+        got = ddp.bucket_layout()
+        assert [b["parameters"] for b in got] == [e[2] for e in want], (s, got)
+        assert [b["offsets"] for b in got] == [e[3] for e in want], s
+        assert [b["numel"] for b in got] == [e[4] for e in want], s
+        loss.backward()
+        assert abs(float(loss.detach()) - float(z[f"loss/{s}/{rank}"])) < 1e-5
+        for i, p in enumerate(params):
+            # averaged gradients: bit-exact on the first step (ws=2: one addition, order-free);
+            # later steps start from parameters a few ulp apart (fused vs default AdamW arithmetic)
+            if s == 0:
+                assert np.array_equal(p.grad.numpy(), z[f"avg_g/{s}/{i}"]), (s, i)
+            else:
+                assert np.allclose(p.grad.numpy(), z[f"avg_g/{s}/{i}"], rtol=1e-3, atol=1e-7), (s, i)
+            if gabv:
+                bk = ddp._bucket_of[i]
+                assert p.grad.data_ptr() == bk.views[bk.spec.indices.index(i)].data_ptr()
+        tn = ddp.clip_grad_norm_(cfg["max_norm"], fused_optimizer=opt)
+        assert abs(float(tn) - float(z[f"norm/{s}"])) <= (1e-6 if s == 0 else 1e-4) * float(tn)
+        opt.step()
+        opt.zero_grad()
+        for i, p in enumerate(params):
+            assert np.allclose(p.detach().numpy(), z[f"p/{s}/{i}"], rtol=2e-6, atol=1e-7), (s, i)
+    st = ddp._get_ddp_logging_data()
+    assert st["has_rebuilt_buckets"] and st["iterations"] == cfg["steps"]
+    assert st["rebuilt_bucket_sizes"] == [e[4] * 4 for e in sorted([e for e in golden_layout if e[0] == 1],
+                                                                   key=lambda e: e[1])]
+    # one pack per bucket per step: 1 + 3*3
+    assert st["pack_launches"] == 1 + 3 * (cfg["steps"] - 1)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("gabv", [False, True])
+def test_ddp_scheduler_reproduces_live_torch_run(native_lib, gabv):
+    mp.spawn(_worker_vs_golden, args=(2, 29641 + int(gabv), gabv), nprocs=2, join=True)
+
+
+def _worker_side_by_side(rank, ws, port):
+    """Stock torch DDP and ours in the same process on the same data: grads bit-exact, including
+    gradient accumulation under no_sync() and a stock communication hook."""
+    _setup(rank, ws, port)
+    import copy
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+    mg = _load_golden_module()
+    torch.manual_seed(0)
+    base = mg.SmallNet()
+    a, b, c = copy.deepcopy(base), copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, bucket_cap_mb=0.008)
+    ours = ddp_b200.DistributedDataParallel(b, bucket_cap_mb=0.008, kernels=OracleKernels())
+    hooked = ddp_b200.DistributedDataParallel(c, bucket_cap_mb=0.008, kernels=OracleKernels())
+    hooked.register_comm_hook(None, default_hooks.allreduce_hook)
+    with pytest.raises(RuntimeError):
+        hooked.register_comm_hook(None, default_hooks.allreduce_hook)
+
+    def lossf(m, s, r):
+        ids, tgt = mg.live_batch(s, r)
+        return torch.nn.functional.cross_entropy(m(ids).flatten(0, 1), tgt.flatten())
+
+    for s in range(3):
+        for m in (ref, ours, hooked):
+            m.zero_grad()
+            with m.no_sync():                      # micro-batch 1: local accumulation only
+                lossf(m, 10 + s, rank).backward()
+            lossf(m, 20 + s, rank).backward()      # micro-batch 2: synchronised
+        for pr, po, ph in zip(a.parameters(), b.parameters(), c.parameters()):
+            assert torch.equal(pr.grad, po.grad), s
+            assert torch.equal(pr.grad, ph.grad), s          # ws=2: g/2 == g*0.5 exactly
+    # state_dict keeps the `module.` prefix of the wrapper
+    assert list(ours.state_dict().keys()) == list(ref.state_dict().keys())
+    # parameters were broadcast from rank 0 at construction
+    torch.manual_seed(100 + rank)
+    d = mg.SmallNet()
+    ddp_b200.DistributedDataParallel(d, kernels=OracleKernels())
+    flat = torch.cat([p.detach().reshape(-1) for p in d.parameters()])
+    gathered = [torch.empty_like(flat) for _ in range(ws)]
+    dist.all_gather(gathered, flat)
+    assert torch.equal(gathered[0], gathered[1])
+    dist.destroy_process_group()
+
+
+def test_ddp_side_by_side_with_stock_torch(native_lib):
+    mp.spawn(_worker_side_by_side, args=(2, 29651), nprocs=2, join=True)
+
+
+def test_adamw_state_dict_and_table_reuse(native_lib):
+    """Single process, oracle backend: state_dict layout equals torch.optim.AdamW's, and the
+    optimizer reuses its segment table when pointers repeat."""
+    sys.path.insert(0, HERE)
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    torch.manual_seed(0)
+    ps = [torch.nn.Parameter(torch.randn(n)) for n in (5, 300, 2049)]
+    pt = [torch.nn.Parameter(p.detach().clone()) for p in ps]
+    ours = ddp_b200.AdamW(ps, lr=1e-2, weight_decay=0.1, kernels=OracleKernels())
+    ref = torch.optim.AdamW(pt, lr=1e-2, weight_decay=0.1)
+    for s in range(3):
+        gs = [torch.randn_like(p) for p in ps]
+        for p, q, g in zip(ps, pt, gs):
+            p.grad = g.clone()
+            q.grad = g.clone()
+        ours.step()
+        ref.step()
+    for p, q in zip(ps, pt):
+        assert torch.allclose(p, q, rtol=2e-6, atol=1e-7)
+    sd, rd = ours.state_dict(), ref.state_dict()
+    assert sd["state"].keys() == rd["state"].keys()
+    for kx in sd["state"]:
+        assert set(sd["state"][kx]) == {"step", "exp_avg", "exp_avg_sq"} == set(rd["state"][kx])
+        assert float(sd["state"][kx]["step"]) == float(rd["state"][kx]["step"]) == 3.0
+    assert set(rd["param_groups"][0]) <= set(sd["param_groups"][0])
+    assert sd["param_groups"][0]["decoupled_weight_decay"] is True
+    # load into a fresh optimizer and continue: same trajectory
+    ours2 = ddp_b200.AdamW(ps, lr=1e-2, weight_decay=0.1, kernels=OracleKernels())
+    ours2.load_state_dict(sd)
+    for p, q in zip(ps, pt):
+        g = torch.ones_like(p)
+        p.grad, q.grad = g.clone(), g.clone()
+    ours2.step()
+    ref.step()
+    for p, q in zip(ps, pt):
+        assert torch.allclose(p, q, rtol=3e-6, atol=1e-7)
+    with pytest.raises(NotImplementedError):
+        ddp_b200.AdamW(ps, amsgrad=True)

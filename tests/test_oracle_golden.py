@@ -1,0 +1,206 @@
+"""Pin the CPU oracle (oracle/ddp_oracle.c) against golden vectors produced by the real torch
+code paths (tests/golden/make_golden.py). CPU only."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+
+def f32(a):
+    return oracle.bf16_bits_to_f32(a) if a.dtype == np.uint16 else a
+
+
+@pytest.fixture(scope="module")
+def layouts(golden_dir):
+    with open(os.path.join(golden_dir, "bucket_layouts.json")) as f:
+        return json.load(f)
+
+
+def test_bucket_assignment_matches_torch_bit_exact(layouts):
+    assert len(layouts) >= 20
+    for c in layouts:
+        # in the fixtures dtype <-> element size is one to one, so the size doubles as the key;
+        # torch receives the tensors already permuted into ready order when an order is given
+        order = c["order"]
+        numel = c["numel"] if order is None else [c["numel"][i] for i in order]
+        es = c["elem_size"] if order is None else [c["elem_size"][i] for i in order]
+        buckets, limits = oracle.bucket_assign(numel, es, c["limits"], keys=es, expect_sparse=c["sparse"],
+                                               tensor_indices=order)
+        assert buckets == c["buckets"], c["name"]
+        assert limits == c["bucket_limits"], c["name"]
+
+
+def test_bucket_tables_of_survey(layouts):
+    """SURVEY.md §8a sizes: GPT-2 13 buckets, Llama-1B 49, 8B 162, 70B-slice 26 (1 MiB / 25 MiB)."""
+    want = {"gpt2-small-fp32": 13, "llama-3.2-1b-bf16": 49, "llama-3.1-8b-bf16": 162,
+            "llama-3.1-70b-4layer-bf16": 26}
+    got = {c["name"].split("/")[0]: len(c["buckets"]) for c in layouts if c["name"].endswith("/rebuild-1MiB-25MiB")}
+    # the survey's tables use the live grad-ready order; reversed registration order (used by the
+    # fixture) gives the same counts for GPT-2 and differs by the position of the norm weights only
+    assert got["gpt2-small-fp32"] == want["gpt2-small-fp32"]
+    for k in want:
+        assert abs(got[k] - want[k]) <= 2, (k, got[k])
+
+
+def test_pack_scale_matches_torch_mul(golden_dir):
+    z = np.load(os.path.join(golden_dir, "pack_scale.npz"))
+    for dt in ("f32", "bf16"):
+        x = z[f"{dt}/x"]
+        for ws in (1, 2, 3, 4, 6, 8):
+            got = oracle.scale_cast(x, x.dtype, np.float32(1.0 / ws))
+            want = z[f"{dt}/ws{ws}"]
+            # NaN-free inputs: compare bit patterns
+            assert np.array_equal(got.view(np.uint16 if dt == "bf16" else np.uint32),
+                                  want.view(np.uint16 if dt == "bf16" else np.uint32)), (dt, ws)
+    assert np.array_equal(oracle.scale_cast(z["f32/x"], np.uint16, 1.0), z["f32_to_bf16"])
+
+
+@pytest.fixture(scope="module")
+def adamw_golden(golden_dir):
+    return np.load(os.path.join(golden_dir, "adamw_steps.npz"))
+
+
+def _replay(z, dt, path_fn, torch_bf16_norm, fold_clip):
+    """clip_grad_norm_ + AdamW with the oracle on the golden inputs; returns (p, m, v, norms)."""
+    sizes = [int(x) for x in z["sizes"]]
+    steps = int(z["steps"])
+    lr, b1, b2, eps, wd = [float(x) for x in z["hp"]]
+    max_norm = float(z["max_norm"])
+    p = [z[f"{dt}/p0/{i}"].copy() for i in range(len(sizes))]
+    m = [np.zeros_like(x) for x in p]
+    v = [np.zeros_like(x) for x in p]
+    norms = []
+    for s in range(steps):
+        g = [z[f"{dt}/g/{s}/{i}"].copy() for i in range(len(sizes))]
+        total, coef = oracle.total_norm_coef([oracle.sumsq(x) for x in g], max_norm, torch_bf16_norm)
+        norms.append(total)
+        for i in range(len(sizes)):
+            if fold_clip:
+                path_fn(p[i], g[i], m[i], v[i], lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=wd,
+                        step=s + 1, clip_coef=coef)
+            else:
+                oracle.scale_inplace(g[i], coef)
+                path_fn(p[i], g[i], m[i], v[i], lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=wd, step=s + 1)
+    return p, m, v, norms
+
+
+def test_default_path_bf16_bit_exact(adamw_golden):
+    """torch's default (single-tensor == foreach) AdamW after clip_grad_norm_, bf16: the oracle's
+    restatement reproduces parameters and both moments BIT FOR BIT over 12 steps."""
+    z = adamw_golden
+    p, m, v, norms = _replay(z, "bf16", oracle.single_tensor_adamw, True, False)
+    for path in ("default", "foreach"):
+        for i in range(len(p)):
+            assert np.array_equal(p[i], z[f"bf16/{path}/p/{i}"]), (path, i)
+            assert np.array_equal(m[i], z[f"bf16/{path}/m/{i}"]), (path, i)
+            assert np.array_equal(v[i], z[f"bf16/{path}/v/{i}"]), (path, i)
+        assert np.array_equal(np.asarray(norms), z[f"bf16/{path}/norms"])
+
+
+def test_default_path_f32_one_ulp(adamw_golden):
+    """fp32: agreement to a few ulp, not bitwise: torch's vectorised CPU sqrt is not correctly
+    rounded in ~0.6 % of lanes (see oracle/ddp_oracle.c), and the clip coefficient inherits the
+    summation order of the norm."""
+    z = adamw_golden
+    p, m, v, norms = _replay(z, "f32", oracle.single_tensor_adamw, False, False)
+    for i in range(len(p)):
+        wp = z[f"f32/default/p/{i}"]
+        assert np.max(np.abs(p[i] - wp)) <= 2e-8          # |p| ~ 0.02: ulp = 1.9e-9
+        assert np.allclose(m[i], z[f"f32/default/m/{i}"], rtol=0, atol=1e-9)
+        assert np.allclose(v[i], z[f"f32/default/v/{i}"], rtol=1e-6, atol=1e-12)
+    assert np.allclose(norms, z["f32/default/norms"], rtol=1e-6)
+
+
+def test_clipped_grad_rounding(adamw_golden):
+    """g * coef as torch leaves it in p.grad (bf16: coef itself is a bf16 tensor)."""
+    z = adamw_golden
+    for dt, bf in (("f32", False), ("bf16", True)):
+        g = [z[f"{dt}/g/0/{i}"].copy() for i in range(3)]
+        _, coef = oracle.total_norm_coef([oracle.sumsq(x) for x in g], float(z["max_norm"]), bf)
+        for i in range(3):
+            oracle.scale_inplace(g[i], coef)
+            want = z[f"{dt}/default/clipped_g0/{i}"]
+            if bf:
+                assert np.array_equal(g[i], want)
+            else:
+                assert np.allclose(g[i], want, rtol=5e-7, atol=0)      # coef off by <= 2 ulp (norm summation order)
+
+
+@pytest.mark.parametrize("dt,tol_p,tol_m,tol_v", [("f32", 2e-7, 5e-9, 2e-10), ("bf16", 1e-3, 2.5e-4, 2e-7)])
+def test_fused_path_within_torch_spread(adamw_golden, dt, tol_p, tol_m, tol_v):
+    """The kernel's arithmetic (oracle_fused_clip_adamw, clip folded in) against torch's three CPU
+    paths. Tolerance = the spread torch shows between its own fused and default paths on these
+    inputs: fp32 max-abs 2e-7 on |p|~0.02; bf16 1e-3 (a few bf16 ulps)."""
+    z = adamw_golden
+    p, m, v, _ = _replay(z, dt, oracle.fused_clip_adamw, dt == "bf16", True)
+    for path in ("default", "fused"):
+        for i in range(len(p)):
+            assert np.max(np.abs(f32(p[i]) - f32(z[f"{dt}/{path}/p/{i}"]))) <= tol_p, (path, i)
+            assert np.max(np.abs(f32(m[i]) - f32(z[f"{dt}/{path}/m/{i}"]))) <= tol_m, (path, i)
+            assert np.max(np.abs(f32(v[i]) - f32(z[f"{dt}/{path}/v/{i}"]))) <= tol_v, (path, i)
+    # and torch's own spread on the same data, for the record
+    spread = max(np.max(np.abs(f32(z[f"{dt}/fused/p/{i}"]) - f32(z[f"{dt}/default/p/{i}"]))) for i in range(3))
+    assert spread <= tol_p
+
+
+def test_live_ddp_chain(golden_dir):
+    """Whole path against a live 2-rank gloo DistributedDataParallel + clip_grad_norm_ + AdamW run:
+    local grads of both ranks -> scale by 1/2 -> sum -> norm -> clip -> AdamW, 4 steps, fp32.
+    torch ran its default AdamW path there, the oracle the fused arithmetic: a few fp32 ulp apart."""
+    z = np.load(os.path.join(golden_dir, "ddp_live.npz"))
+    cfg = json.loads(str(z["cfg"]))
+    numel = [int(x) for x in z["numel"]]
+    ws, steps = cfg["world_size"], cfg["steps"]
+    p = [z[f"p0/{i}"].copy().reshape(-1) for i in range(len(numel))]
+    m = [np.zeros_like(x) for x in p]
+    v = [np.zeros_like(x) for x in p]
+    p2 = [x.copy() for x in p]          # same chain through the default-path restatement
+    m2 = [np.zeros_like(x) for x in p]
+    v2 = [np.zeros_like(x) for x in p]
+    hp = dict(lr=cfg["lr"], beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
+    for s in range(steps):
+        avg = []
+        for i in range(len(numel)):
+            parts = [oracle.scale_cast(z[f"local_g/{s}/{r}/{i}"].reshape(-1), np.float32, np.float32(1.0 / ws))
+                     for r in range(ws)]
+            a = parts[0] + parts[1]
+            assert np.array_equal(a, z[f"avg_g/{s}/{i}"].reshape(-1)), (s, i)   # ws=2: order-free, exact
+            avg.append(a)
+        total, coef = oracle.total_norm_coef([oracle.sumsq(g) for g in avg], cfg["max_norm"], False)
+        assert abs(total - float(z[f"norm/{s}"])) <= 1e-6 * total
+        for i in range(len(numel)):
+            want = z[f"p/{s}/{i}"].reshape(-1)
+            oracle.fused_clip_adamw(p[i], avg[i], m[i], v[i], step=s + 1, clip_coef=coef, **hp)
+            # fused arithmetic vs torch's default path: p*(1-lr*wd) carries the representation
+            # error of float(1-lr*wd), the fused fma does not -> ~2 ulp per step at |p|~1
+            assert np.allclose(p[i], want, rtol=2e-6, atol=1e-7), (s, i)
+            g2 = avg[i].copy()
+            oracle.scale_inplace(g2, coef)
+            oracle.single_tensor_adamw(p2[i], g2, m2[i], v2[i], step=s + 1, **hp)
+            assert np.allclose(p2[i], want, rtol=2e-6, atol=3e-8), (s, i)   # 1-ulp effects of the norm's summation order
+
+
+def test_live_ddp_layout_matches_planner(golden_dir):
+    """Bucket membership and element offsets observed in the live DDP run (via a comm hook) equal
+    the oracle planner's: iteration 0 one bucket in registration order; afterwards rebuilt in
+    grad-ready order with [cap, cap] limits (bucket_cap_mb was given explicitly)."""
+    z = np.load(os.path.join(golden_dir, "ddp_live.npz"))
+    cfg = json.loads(str(z["cfg"]))
+    numel = [int(x) for x in z["numel"]]
+    layout = json.loads(str(z["layout"]))
+    it0 = [e for e in layout if e[0] == 0]
+    assert len(it0) == 1 and it0[0][2] == list(range(len(numel)))
+    assert it0[0][3] == list(np.cumsum([0] + numel[:-1]))
+    it1 = sorted([e for e in layout if e[0] == 1], key=lambda e: e[1])
+    ready = [pi for e in it1 for pi in e[2]]
+    cap = int(cfg["bucket_cap_mb"] * 1024 * 1024)
+    buckets, _ = oracle.bucket_assign([numel[i] for i in ready], [4] * len(ready), [cap, cap], tensor_indices=ready)
+    assert buckets == [e[2] for e in it1]
+    for e in it1:
+        offs = list(np.cumsum([0] + [numel[i] for i in e[2]][:-1]))
+        assert e[3] == offs and e[4] == sum(numel[i] for i in e[2])
+    for s in range(2, cfg["steps"]):
+        assert [e[2] for e in sorted([e for e in layout if e[0] == s], key=lambda e: e[1])] == buckets
