@@ -1,0 +1,453 @@
+#!/usr/bin/env python
+"""bench.py — the DDP gradient-sync + clip + AdamW hot path on B200.
+
+A *step* is one pass of the hot path over one set of synthetic gradients for the Llama-3.2-1B
+architecture in bf16 (BASELINE.json configs[1]: 146 parameter tensors, 1,235,814,400 elements):
+per bucket pack (flatten + 1/world_size + cast) -> NCCL allreduce on a side stream (N>1) ->
+per-tensor sum of squares; then total norm + clip coefficient on the device; then ONE fused
+clip+AdamW launch over all parameters. Forward/backward of the model are not part of the path
+(SURVEY.md §8f-2 lists them as the next row).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N>1 is launched by torchrun (one rank per GPU, NCCL). Prints ONE JSON line on rank 0.
+--impl reference times the reference's own CPU implementation of the same path: the UNMODIFIED
+stock torch code (DistributedDataParallel on gloo + clip_grad_norm_ + torch.optim.AdamW) on the
+box's host cores, fed the same synthetic gradients through autograd.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import socket
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+METRIC = "ddp_hot_path_steps_per_s"
+UNIT = "steps/s x ranks (one step = grad-sync + clip + AdamW over all parameters of one replica)"
+MAX_NORM = 1.0
+LR = 5e-5
+
+
+# ---- workload --------------------------------------------------------------------------------
+def llama_param_shapes(hidden, layers, heads, kv_heads, inter, vocab, tie):
+    """Parameter shapes of transformers' LlamaForCausalLM in DDP registration order
+    (tests/test_workload_shapes.py checks them against the golden numel lists)."""
+    hd = hidden // heads
+    shapes = [(vocab, hidden)]
+    for _ in range(layers):
+        shapes += [(hidden, hidden), (kv_heads * hd, hidden), (kv_heads * hd, hidden), (hidden, hidden),
+                   (inter, hidden), (inter, hidden), (hidden, inter), (hidden,), (hidden,)]
+    shapes.append((hidden,))
+    if not tie:
+        shapes.append((vocab, hidden))
+    return shapes
+
+
+WORKLOADS = {
+    "llama-3.2-1b": dict(hidden=2048, layers=16, heads=32, kv_heads=8, inter=8192, vocab=128256, tie=True),
+    "llama-3.1-8b": dict(hidden=4096, layers=32, heads=32, kv_heads=8, inter=14336, vocab=128256, tie=False),
+    "llama-3.1-70b-4layer": dict(hidden=8192, layers=4, heads=64, kv_heads=8, inter=28672, vocab=128256, tie=False),
+    "tiny": dict(hidden=256, layers=2, heads=8, kv_heads=2, inter=512, vocab=1024, tie=True),
+}
+
+
+def grad_ready_order(n_params, layers, tie):
+    """Order in which a Llama backward makes gradients ready (SURVEY.md §8a probe): [lm_head,] final
+    norm, then per layer from the last: down, up, gate, post_attn_ln, o, v, k, q, input_ln; embed last."""
+    order = []
+    if not tie:
+        order.append(n_params - 1)
+    order.append(1 + 9 * layers)
+    for l in range(layers - 1, -1, -1):
+        b = 1 + 9 * l
+        order += [b + 6, b + 5, b + 4, b + 8, b + 3, b + 2, b + 1, b + 0, b + 7]
+    order.append(0)
+    return order
+
+
+class ParamSet(torch.nn.Module):
+    """The parameter tensors of the model, without its forward: the hot path only needs them."""
+
+    def __init__(self, shapes, dtype, device, seed=0):
+        super().__init__()
+        g = torch.Generator(device=device).manual_seed(seed)
+        self.ps = torch.nn.ParameterList(
+            [torch.nn.Parameter(torch.empty(s, dtype=dtype, device=device).normal_(0, 0.02, generator=g))
+             for s in shapes])
+
+
+class SynthGrad(torch.autograd.Function):
+    """loss = SynthGrad(*params): backward hands each parameter its preset synthetic gradient, so the
+    stock autograd -> AccumulateGrad -> DDP-hook machinery runs exactly as in training."""
+
+    @staticmethod
+    def forward(ctx, holder, *params):
+        ctx.holder = holder
+        return params[0].new_zeros(())
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        return (None,) + tuple(ctx.holder["grads"])
+
+
+# ---- helpers ----------------------------------------------------------------------------------
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.path = gpu_index, None, f"/tmp/ddpb200_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def measured_peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (torch copy_, read+write)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def adamw_traffic_from_profile():
+    """dram bytes per launch of the fused clip+AdamW kernel from the committed ncu summary, if any."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "adamw_ncu_summary.json")))
+        return d.get("dram_bytes_per_launch_llama_1b")
+    except Exception:
+        return None
+
+
+# ---- our arm ------------------------------------------------------------------------------------
+def run_ours(args):
+    import ddp_b200
+
+    rank = int(os.environ.get("RANK", 0))
+    ws = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    assert ws == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={ws} (launch N>1 with torchrun)"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if "MASTER_ADDR" not in os.environ:
+        os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(free_port())
+    dist.init_process_group("nccl", rank=rank, world_size=ws, device_id=dev)
+
+    cfg = WORKLOADS[args.workload]
+    shapes = llama_param_shapes(**cfg)
+    dtype = torch.bfloat16
+    model = ParamSet(shapes, dtype, dev)
+    params = list(model.parameters())
+    numel = [p.numel() for p in params]
+    total = sum(numel)
+    esize = 2
+    ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
+    opt = ddp_b200.AdamW(params, lr=LR, weight_decay=1e-2)
+
+    # synthetic gradients, resident in HBM, one tensor per parameter (rank-dependent values)
+    gflat = torch.empty(total, dtype=dtype, device=dev).normal_(0, 0.01, generator=torch.Generator(device=dev).manual_seed(1 + rank))
+    offs = [0]
+    for n in numel[:-1]:
+        offs.append(offs[-1] + n)
+    grads = [gflat[o:o + n].view(s) for o, n, s in zip(offs, numel, shapes)]
+    order = grad_ready_order(len(params), cfg["layers"], cfg["tie"])
+
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
+    norm_host = torch.empty(2, dtype=torch.float32).pin_memory()
+
+    def step(i=None, first=False):
+        ddp.reduce_gradients(grads, order=order if first else None)
+        ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
+        if i is not None:
+            ev[i][0].record()
+        opt.step()
+        if i is not None:
+            ev[i][1].record()
+        opt.zero_grad()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if ws > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    step(first=True)                    # iteration 0: one bucket, records the ready order
+    for _ in range(max(args.warmup, 3)):
+        step()                          # rebuilt buckets from here on
+    stats0 = dict(ddp._get_ddp_logging_data())
+
+    # ---- timed: inputs resident in HBM -----------------------------------------------------------
+    clocks = ClockSampler(local)
+    sync_all()
+    if rank == 0:
+        clocks.start()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(args.steps):
+        step(i)
+    t1.record()
+    sync_all()
+    clk = clocks.stop() if rank == 0 else None
+    ms = t0.elapsed_time(t1)
+    adamw_ms = statistics.mean(a.elapsed_time(b) for a, b in ev)
+    stats1 = dict(ddp._get_ddp_logging_data())
+    launches = sum(stats1[k] - stats0[k] for k in ("pack_launches", "norm_launches", "unpack_launches"))
+    launches += args.steps * (1 + opt.launches_last_step)          # finalize + fused AdamW per step
+    allreduces = stats1["allreduces"] - stats0["allreduces"]
+
+    # ---- timed: end to end from HOST gradients ---------------------------------------------------
+    # the gradients of the step arrive from pinned host memory (H2D inside the timed region), the
+    # result read back is the pre-clip total norm (D2H, then a host read).
+    e2e_steps = max(2, min(args.steps, 10))
+    host_g = torch.empty(total, dtype=dtype).pin_memory()
+    host_g.copy_(gflat)
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    last_norm = 0.0
+    for _ in range(e2e_steps):
+        gflat.copy_(host_g, non_blocking=True)
+        ddp.reduce_gradients(grads)
+        ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
+        norm_host.copy_(ddp._norm_out, non_blocking=True)
+        opt.step()
+        opt.zero_grad()
+        torch.cuda.current_stream().synchronize()
+        last_norm = float(norm_host[0])
+    e1.record()
+    sync_all()
+    e2e_ms = e0.elapsed_time(e1)
+
+    t = torch.tensor([ms, e2e_ms, adamw_ms], dtype=torch.float64, device=dev)
+    if ws > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms, adamw_ms = [float(x) for x in t.tolist()]
+
+    out = None
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        alg_bytes = 14 * total                                       # bf16 p,g,m,v read + p,m,v write
+        achieved = alg_bytes / (adamw_ms * 1e-3) / 1e9
+        bucket_bytes = stats1["bucket_sizes"]
+        out = {
+            "metric": METRIC, "value": ws * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ws,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic", "impl": "ours",
+            "config": {"workload": f"{args.workload}-arch parameter set, bf16 p/g/m/v, {len(params)} tensors, "
+                                   f"{total} elements; gradient_as_bucket_view, 25 MiB buckets "
+                                   f"({len(bucket_bytes)} after rebuild), max_norm {MAX_NORM}, AdamW lr {LR}",
+                       "global_batch": f"{ws} replicas x 1 synthetic gradient set",
+                       "l2": "working set per step 12.4 GB >> 126 MB L2; no flush needed",
+                       "parallelism": f"dp{ws}"},
+            "steps_per_s": args.steps / (ms * 1e-3),
+            "e2e": {"value": ws * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "steps": e2e_steps,
+                    "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8,
+                    "note": "gradients of each step copied from pinned host memory; total norm read back"},
+            "gpu_launches": launches,
+            "nccl_allreduces": allreduces,
+            "roofline": {"kernel": "adamw_kernel (fused clip+AdamW, bf16)", "bound": "hbm", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                         "frac_of_8000_nominal": achieved / 8000.0, "algorithmic_bytes_per_launch": alg_bytes,
+                         "avg_launch_ms": adamw_ms, "traffic": adamw_traffic_from_profile()},
+            "path_bytes_per_step": {"pack": 4 * total, "norm": 0 if ws == 1 else 2 * total, "adamw": 14 * total},
+            "path_gbs": (4 * total + (0 if ws == 1 else 2 * total) + 14 * total) / (ms / args.steps * 1e-3) / 1e9,
+            "clocks": clk, "total_norm": last_norm,
+        }
+        if ws > 1:
+            # bucket allreduce bus bandwidth, measured alone on the same buckets (NCCL-tests convention)
+            out["allreduce"] = measure_allreduce(ddp, ws, dev)
+    elif ws > 1:
+        measure_allreduce(ddp, ws, dev)
+
+    if rank == 0 and ws == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline_sample(cfg, total)
+    if rank == 0:
+        print(json.dumps(out))
+    dist.destroy_process_group()
+
+
+def measure_allreduce(ddp, ws, dev):
+    """busbw = S/t * 2(n-1)/n over the model's own buckets, back to back on one stream."""
+    bufs = [bk.buffer for bk in ddp._buckets]
+    S = sum(b.numel() * b.element_size() for b in bufs)
+    for _ in range(2):
+        for b in bufs:
+            dist.all_reduce(b)
+    torch.cuda.synchronize()
+    dist.barrier()
+    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    reps = 5
+    for _ in range(reps):
+        for b in bufs:
+            dist.all_reduce(b)
+    b_.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b_) / reps], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t)
+    for b in bufs:
+        b.zero_()
+    bus = S / (ms * 1e-3) * 2 * (ws - 1) / ws / 1e9
+    return {"bytes_per_step": S, "ms_per_step": ms, "busbw_gbs": bus, "frac_of_900": bus / 900.0,
+            "buckets": len(bufs)}
+
+
+# ---- CPU baselines --------------------------------------------------------------------------------
+def stock_cpu_step_rate(cfg, steps, warmup, layers_sample=None):
+    """Stock torch on the host cores: DistributedDataParallel (gloo, 1 rank) + clip_grad_norm_ +
+    torch.optim.AdamW, gradients delivered through autograd. Returns (steps/s on the sample,
+    sample elements, threads)."""
+    c = dict(cfg)
+    if layers_sample is not None:
+        c["layers"] = layers_sample
+    shapes = llama_param_shapes(**c)
+    model = ParamSet(shapes, torch.bfloat16, torch.device("cpu"))
+    params = list(model.parameters())
+    total = sum(p.numel() for p in params)
+    own = not dist.is_initialized()
+    if own:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ["MASTER_PORT"] = str(free_port())
+        dist.init_process_group("gloo", rank=0, world_size=1)
+        pg = None
+    else:
+        pg = dist.new_group(ranks=[dist.get_rank()], backend="gloo")
+    ddp = torch.nn.parallel.DistributedDataParallel(model, process_group=pg)
+    opt = torch.optim.AdamW(params, lr=LR, weight_decay=1e-2)
+    holder = {"grads": [torch.empty_like(p).normal_(0, 0.01) for p in params]}
+
+    # ParamSet has no forward of its own: the synthetic-gradient function stands in for the model
+    model.forward = lambda: SynthGrad.apply(holder, *params)
+
+    def one():
+        loss = ddp()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, MAX_NORM)
+        opt.step()
+        opt.zero_grad()
+
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    if own:
+        dist.destroy_process_group()
+    return steps / dt, total, torch.get_num_threads()
+
+
+def cpu_baseline_sample(cfg, total_full):
+    """Bounded sample beside our N=1 number: stock torch CPU path on a 4-decoder-layer slice of the
+    same architecture (embedding included), scaled by elements to the full parameter set."""
+    rate, n, threads = stock_cpu_step_rate(cfg, steps=3, warmup=1, layers_sample=4)
+    return {"value": rate * n / total_full, "unit": UNIT, "cores": threads, "kind": "reference",
+            "sample": f"stock torch DDP(gloo,1 rank)+clip_grad_norm_+AdamW on CPU, bf16, 4-layer slice "
+                      f"({n} of {total_full} elements), 3 steps after 1 warm-up; scaled by element count",
+            "measured_steps_per_s_on_sample": rate, "host_cpus": os.cpu_count()}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    cfg = WORKLOADS[args.workload]
+    total_full = sum(int(torch.Size(s).numel()) for s in llama_param_shapes(**cfg))
+    # bounded: the whole run must end within minutes on host cores -> 4-layer slice, scaled by elements
+    layers = 4 if cfg["layers"] > 4 else None
+    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    rate, n, threads = stock_cpu_step_rate(cfg, steps=steps, warmup=warmup, layers_sample=layers)
+    value = rate * n / total_full
+    sample = (f"stock torch DDP(gloo,1 rank)+clip_grad_norm_+AdamW(default) on CPU, bf16, "
+              f"{'4-layer slice' if layers else 'full model'} ({n} of {total_full} elements), {steps} steps after "
+              f"{warmup} warm-up; scaled by element count")
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+           "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "bf16", "data": "synthetic", "impl": "reference",
+           "config": {"workload": f"{args.workload}-arch parameter set, bf16 p/g/m/v", "parallelism": "cpu"},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample,
+                            "host_cpus": os.cpu_count()},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=list(WORKLOADS), default="llama-3.2-1b")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,126 @@
+"""GPU tests of the whole step through the public classes: ours (DistributedDataParallel +
+clip_grad_norm_ + AdamW on the sm_100a kernels) beside stock torch (DDP + clip_grad_norm_ +
+AdamW(fused=True)) on the same model, weights and batches. Single GPU with a 1-rank NCCL group,
+and a 2-rank NCCL run when the box has two GPUs."""
+import copy
+import importlib.util
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def _golden_module():
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(HERE, "golden", "make_golden.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _train_compare(rank, ws, dtype, gabv, steps=5, fold_clip=True):
+    import ddp_b200
+    mg = _golden_module()
+    dev = torch.device("cuda", rank if ws > 1 else 0)
+    torch.manual_seed(0)
+    base = mg.SmallNet().to(dev).to(dtype)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, device_ids=[dev.index], bucket_cap_mb=0.008,
+                                                    gradient_as_bucket_view=gabv)
+    ours = ddp_b200.DistributedDataParallel(b, device_ids=[dev.index], bucket_cap_mb=0.008,
+                                            gradient_as_bucket_view=gabv)
+    o_ref = torch.optim.AdamW(a.parameters(), lr=1e-2, fused=True)
+    o_our = ddp_b200.AdamW(b.parameters(), lr=1e-2)
+    for s in range(steps):
+        ids, tgt = mg.live_batch(s, rank)          # CPU tensors: DDP moves them (device_ids given)
+        for m, o, mine in ((ref, o_ref, False), (ours, o_our, True)):
+            loss = torch.nn.functional.cross_entropy(m(ids).flatten(0, 1).float(), tgt.to(dev).flatten())
+            loss.backward()
+            if s == 0:
+                first_loss = float(loss.detach())
+            if mine:
+                tn = ours.clip_grad_norm_(0.5, fused_optimizer=o_our if fold_clip else None)
+            else:
+                tn_ref = torch.nn.utils.clip_grad_norm_(a.parameters(), 0.5)
+            o.step()
+            o.zero_grad()
+        rel = 2 ** -6 if dtype == torch.bfloat16 else 1e-4
+        assert abs(float(tn) - float(tn_ref)) <= rel * float(tn_ref) * (1 + s), (s, float(tn), float(tn_ref))
+        if s >= 1:
+            # layouts after the rebuild: same buckets as the stock reducer built
+            want = ref._get_ddp_logging_data().get("rebuilt_bucket_sizes", "")
+            got = ours._get_ddp_logging_data()["rebuilt_bucket_sizes"]
+            assert ", ".join(str(x) for x in got) == str(want)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        d = (pa.float() - pb.float()).abs()
+        if dtype == torch.float32:
+            assert float(d.max()) <= 2e-5, float(d.max())         # 5 steps at lr 1e-2, |p| up to ~3
+        else:
+            assert float(d.max()) <= 0.1 and float(d.mean()) <= 4e-3, (float(d.max()), float(d.mean()))
+    return first_loss
+
+
+@pytest.fixture(scope="module")
+def pg1():
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = "29661"
+    torch.cuda.set_device(0)
+    dist.init_process_group("nccl", rank=0, world_size=1)
+    yield
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("gabv", [False, True])
+def test_single_gpu_step_matches_stock_torch(pg1, dtype, gabv):
+    _train_compare(0, 1, dtype, gabv)
+
+
+def test_single_gpu_unfolded_clip_scales_grads_in_place(pg1):
+    _train_compare(0, 1, torch.float32, True, steps=3, fold_clip=False)
+    _train_compare(0, 1, torch.float32, False, steps=3, fold_clip=False)
+
+
+def test_reduce_gradients_entry_and_stats(pg1):
+    """The manual gradient feed used by bench.py drives the same scheduler as a real backward."""
+    import ddp_b200
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(1)
+    net = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.Linear(128, 64)).to(dev).to(torch.bfloat16)
+    ddp = ddp_b200.DistributedDataParallel(net, bucket_cap_mb=0.01, gradient_as_bucket_view=True)
+    params = list(net.parameters())
+    grads = [torch.randn_like(p) for p in params]
+    ddp.reduce_gradients([g.clone() for g in grads])
+    ddp.reduce_gradients([g.clone() for g in grads])           # second call: rebuilt buckets
+    assert ddp._get_ddp_logging_data()["has_rebuilt_buckets"]
+    for p, g in zip(params, grads):
+        assert torch.equal(p.grad, g)                           # ws=1: averaging is the identity
+    want = torch.nn.utils.get_total_norm(grads)
+    got = ddp.clip_grad_norm_(1e9)
+    assert abs(float(got) - float(want)) <= 2 ** -7 * float(want)
+
+
+def _two_rank_worker(rank, ws, port):
+    for p in (ROOT, HERE):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=ws)
+    for dtype in (torch.float32, torch.bfloat16):
+        for gabv in (False, True):
+            _train_compare(rank, ws, dtype, gabv)
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (gpurun --gpus 2)")
+def test_two_gpu_nccl_step_matches_stock_torch():
+    mp.spawn(_two_rank_worker, args=(2, 29671), nprocs=2, join=True)
