@@ -8,59 +8,108 @@
 // bit for bit. The bias corrections 1 - beta^step are computed once on the host, in double from
 // the fp32-rounded betas, and rounded to fp32 (fused_adam_utils.cuh:131-150 takes the same
 // power on the device in fp32).
+//
+// What the first ncu capture (profiles/r01_*) showed and what was done about it:
+//   * 57 issue slots per element, 67 % issue-slot utilisation at 5.5 TB/s: the kernel was close to
+//     issue-bound. The option flags (clip / grad_scale / maximize / store-grad / weight-decay) are
+//     therefore compile-time in the common cases (FAST modes), and sqrt(v)/sqrt(bc2) — a division
+//     by a per-launch constant — uses the exact 3-instruction reciprocal+residual form
+//     (div_by_const, common.cuh) instead of the ~10-instruction IEEE division sequence.
+//   * 256-bit global accesses with L2 evict-first (sm_100a) halve the LSU instruction count.
 #include <math.h>
+#include <stdlib.h>
 #include "launch.cuh"
 
 namespace ddpb200 {
 
 struct AdamScalars {
-  float lr, beta1, beta2, eps, lr_wd_valid;  // lr_wd_valid: 1 if weight decay is applied
-  float weight_decay, bc1, bc2_sqrt;
+  float lr, beta1, beta2, eps, weight_decay, bc1, bc2_sqrt, rcp_bc2_sqrt;
 };
 
-template <int PDT, int GDT, int SDT> struct AdamGroup {
-  static constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
-  static constexpr int G = any_f32 ? 4 : 8;
-  static constexpr int U = 8 / G;
+// MODE: how the per-launch options reach the element function
+constexpr int kModeGeneral  = 0;  // runtime flags (grad_scale, maximize, store-grad, wd==0, unrounded clip)
+constexpr int kModeFastClip = 1;  // clip * round-to-grad-dtype, weight decay on, nothing else
+constexpr int kModeFastPlain = 2; // no clip, weight decay on, nothing else
+
+struct AdamRuntime {
+  float lr_wd, step_size, grad_scale, clip;
+  bool has_scale, has_clip, round_clip, maximize, has_wd;
 };
 
-// one element; p, m, v updated in place, g returns the value to store back (if asked)
-template <int GDT>
-__device__ __forceinline__ void adamw_elem(float& p, float& g, float& m, float& v,
-                                           const AdamScalars& a, float lr_wd, float step_size,
-                                           float inv_scale_valid, float grad_scale,
-                                           float clip_valid, float clip_coef, uint32_t flags) {
-  if (inv_scale_valid != 0.f) g = __fdiv_rn(g, grad_scale);
-  if (clip_valid != 0.f) {
-    g = __fmul_rn(g, clip_coef);
-    if (flags & DDPB200_ADAMW_ROUND_CLIPPED_GRAD) g = round_through<GDT>(g);
+template <int GDT, int MODE>
+__device__ __forceinline__ void adamw_elem(float& p, float& g, float& m, float& v, const AdamScalars& a,
+                                           const AdamRuntime& r) {
+  float gm;
+  if constexpr (MODE == kModeGeneral) {
+    if (r.has_scale) g = __fdiv_rn(g, r.grad_scale);
+    if (r.has_clip) {
+      g = __fmul_rn(g, r.clip);
+      if (r.round_clip) g = round_through<GDT>(g);
+    }
+    gm = r.maximize ? -g : g;
+    if (r.has_wd) p = __fmaf_rn(-r.lr_wd, p, p);
+  } else {
+    if constexpr (MODE == kModeFastClip) g = round_through<GDT>(__fmul_rn(g, r.clip));
+    gm = g;
+    p = __fmaf_rn(-r.lr_wd, p, p);                                   // p -= lr*wd*p
   }
-  float gm = (flags & DDPB200_ADAMW_MAXIMIZE) ? -g : g;
-  if (a.lr_wd_valid != 0.f) p = __fmaf_rn(-lr_wd, p, p);            // p -= lr*wd*p
   m = __fmaf_rn(a.beta1, m, __fmaf_rn(-a.beta1, gm, gm));            // lerp(m, g, 1-b1)
   const float gg = __fmul_rn(gm, gm);
   v = __fmaf_rn(a.beta2, v, __fmaf_rn(-a.beta2, gg, gg));
-  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), a.bc2_sqrt), a.eps);
-  p = __fsub_rn(p, __fdiv_rn(__fmul_rn(step_size, m), denom));
+  const float denom = __fadd_rn(div_by_const(__fsqrt_rn(v), a.bc2_sqrt, a.rcp_bc2_sqrt), a.eps);
+  p = __fsub_rn(p, __fdiv_rn(__fmul_rn(r.step_size, m), denom));
 }
 
-template <class Tab, int PDT, int GDT, int SDT>
-__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+// One chunk through G-element groups (vector accesses); returns how many elements were done, the
+// ragged end is left to the caller's scalar loop.
+template <int PDT, int GDT, int SDT, int MODE, int VECB>
+__device__ __forceinline__ int64_t adamw_chunk_vec(char* P, char* Gp, char* M, char* V, int64_t len,
+                                                   const AdamScalars& a, const AdamRuntime& r, bool store_g) {
+  constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
+  constexpr int G = GroupSize<VECB, any_f32>::G;
+  const int64_t groups_end = len / G * G;
+#pragma unroll 1
+  for (int64_t i = (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
+    float p[G], g[G], m[G], v[G];
+    GroupIO<GDT, G>::load(Gp, i, g);
+    GroupIO<PDT, G>::load(P, i, p);
+    GroupIO<SDT, G>::load(M, i, m);
+    GroupIO<SDT, G>::load(V, i, v);
+#pragma unroll
+    for (int k = 0; k < G; ++k) adamw_elem<GDT, MODE>(p[k], g[k], m[k], v[k], a, r);
+    GroupIO<PDT, G>::store(P, i, p);
+    GroupIO<SDT, G>::store(M, i, m);
+    GroupIO<SDT, G>::store(V, i, v);
+    if (MODE == kModeGeneral && store_g) GroupIO<GDT, G>::store(Gp, i, g);
+  }
+  return groups_end;
+}
+
+template <int PDT, int GDT, int SDT, int G>
+__device__ __forceinline__ bool all_aligned(const void* P, const void* Gp, const void* M, const void* V) {
+  return group_aligned<PDT, G>(P) && group_aligned<GDT, G>(Gp) && group_aligned<SDT, G>(M) &&
+         group_aligned<SDT, G>(V);
+}
+
+template <class Tab, int PDT, int GDT, int SDT, int MODE, int CT>
+__global__ void __launch_bounds__(kThreads, CT)
 adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
              AdamScalars a, const float* __restrict__ lr_ptr, const float* __restrict__ clip_ptr,
              const float* __restrict__ grad_scale_ptr, const float* __restrict__ found_inf_ptr,
              uint32_t flags) {
-  constexpr int G = AdamGroup<PDT, GDT, SDT>::G;
-  constexpr int U = AdamGroup<PDT, GDT, SDT>::U;
-
+  constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
   if (found_inf_ptr && __ldg(found_inf_ptr) == 1.0f) return;      // GradScaler skip (cuh:137-139)
   if (lr_ptr) a.lr = __ldg(lr_ptr);
-  const float lr_wd = __fmul_rn(a.lr, a.weight_decay);
-  const float step_size = __fdiv_rn(a.lr, a.bc1);
-  const float gs_valid = grad_scale_ptr ? 1.f : 0.f;
-  const float gs = grad_scale_ptr ? __ldg(grad_scale_ptr) : 1.f;
-  const float cl_valid = clip_ptr ? 1.f : 0.f;
-  const float cl = clip_ptr ? __ldg(clip_ptr) : 1.f;
+  AdamRuntime r;
+  r.lr_wd = __fmul_rn(a.lr, a.weight_decay);
+  r.step_size = __fdiv_rn(a.lr, a.bc1);
+  r.has_scale = grad_scale_ptr != nullptr;
+  r.grad_scale = r.has_scale ? __ldg(grad_scale_ptr) : 1.f;
+  r.has_clip = clip_ptr != nullptr;
+  r.clip = r.has_clip ? __ldg(clip_ptr) : 1.f;
+  r.round_clip = (flags & DDPB200_ADAMW_ROUND_CLIPPED_GRAD) != 0;
+  r.maximize = (flags & DDPB200_ADAMW_MAXIMIZE) != 0;
+  r.has_wd = a.weight_decay != 0.f;
   const bool store_g = (flags & DDPB200_ADAMW_STORE_GRAD) != 0;
   const int64_t chunk_base = tab.begin(0);
 
@@ -74,63 +123,24 @@ adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chun
     char* M = static_cast<char*>(tab.ptr(s, 2)) + start * ElemOf<SDT>::size;
     char* V = static_cast<char*>(tab.ptr(s, 3)) + start * ElemOf<SDT>::size;
 
-    const bool vec = group_aligned<PDT, G>(P) && group_aligned<GDT, G>(Gp) &&
-                     group_aligned<SDT, G>(M) && group_aligned<SDT, G>(V);
-    int64_t scalar_from = 0;
-    if (vec) {
-      const int64_t full = len / kTileElems * kTileElems;
-      for (int64_t t0 = 0; t0 < full; t0 += kTileElems) {
-        float p[U][G], g[U][G], m[U][G], v[U][G];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int64_t i = t0 + u * (kThreads * G) + threadIdx.x * G;
-          GroupIO<GDT, G>::load(Gp, i, g[u]);
-          GroupIO<PDT, G>::load(P, i, p[u]);
-          GroupIO<SDT, G>::load(M, i, m[u]);
-          GroupIO<SDT, G>::load(V, i, v[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int64_t i = t0 + u * (kThreads * G) + threadIdx.x * G;
-#pragma unroll
-          for (int k = 0; k < G; ++k)
-            adamw_elem<GDT>(p[u][k], g[u][k], m[u][k], v[u][k], a, lr_wd, step_size, gs_valid, gs,
-                            cl_valid, cl, flags);
-          GroupIO<PDT, G>::store(P, i, p[u]);
-          GroupIO<SDT, G>::store(M, i, m[u]);
-          GroupIO<SDT, G>::store(V, i, v[u]);
-          if (store_g) GroupIO<GDT, G>::store(Gp, i, g[u]);
-        }
-      }
-      const int64_t groups_end = len / G * G;
-      for (int64_t i = full + (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
-        float p[G], g[G], m[G], v[G];
-        GroupIO<GDT, G>::load(Gp, i, g);
-        GroupIO<PDT, G>::load(P, i, p);
-        GroupIO<SDT, G>::load(M, i, m);
-        GroupIO<SDT, G>::load(V, i, v);
-#pragma unroll
-        for (int k = 0; k < G; ++k)
-          adamw_elem<GDT>(p[k], g[k], m[k], v[k], a, lr_wd, step_size, gs_valid, gs, cl_valid, cl, flags);
-        GroupIO<PDT, G>::store(P, i, p);
-        GroupIO<SDT, G>::store(M, i, m);
-        GroupIO<SDT, G>::store(V, i, v);
-        if (store_g) GroupIO<GDT, G>::store(Gp, i, g);
-      }
-      scalar_from = groups_end;
-    }
-    for (int64_t i = scalar_from + threadIdx.x; i < len; i += kThreads) {
+    int64_t done = 0;
+    if (all_aligned<PDT, GDT, SDT, GroupSize<32, any_f32>::G>(P, Gp, M, V))
+      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 32>(P, Gp, M, V, len, a, r, store_g);
+    else if (all_aligned<PDT, GDT, SDT, GroupSize<16, any_f32>::G>(P, Gp, M, V))
+      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 16>(P, Gp, M, V, len, a, r, store_g);
+    // ragged end, or a segment whose base is not even 16-byte aligned (odd offset inside a bucket)
+    for (int64_t i = done + threadIdx.x; i < len; i += kThreads) {
       float p = load1<PDT>(P, i), g = load1<GDT>(Gp, i), m = load1<SDT>(M, i), v = load1<SDT>(V, i);
-      adamw_elem<GDT>(p, g, m, v, a, lr_wd, step_size, gs_valid, gs, cl_valid, cl, flags);
+      adamw_elem<GDT, MODE>(p, g, m, v, a, r);
       store1<PDT>(P, i, p);
       store1<SDT>(M, i, m);
       store1<SDT>(V, i, v);
-      if (store_g) store1<GDT>(Gp, i, g);
+      if (MODE == kModeGeneral && store_g) store1<GDT>(Gp, i, g);
     }
   }
 }
 
-template <int PDT, int GDT, int SDT>
+template <int PDT, int GDT, int SDT, int MODE>
 static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int64_t total_chunks,
                         int64_t chunk_elems, const AdamScalars& a, const float* lr_ptr,
                         const float* clip, const float* grad_scale, const float* found_inf,
@@ -139,10 +149,17 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
     [&](auto& tab, int64_t chunks, int64_t, int64_t) -> int {
       using Tab = std::remove_reference_t<decltype(tab)>;
       int err = 0;
-      const int grid = persistent_grid(chunks, &err);
+      const int sms = sm_count_cached(&err);
       if (err) return err;
+      // CTAs per SM, measured on B200 at Llama-1B size (tools/kbench.py, profiles/r01_kbench.txt):
+      // all-bf16 fast modes peak at 3 (6.3 TB/s; 2 -> 5.6, 4 -> 5.0 with spills); anything with an
+      // fp32 stream, and the general mode, peak at 2 (6.6 TB/s fp32).
+      constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
+      constexpr int CT = (!any_f32 && MODE != kModeGeneral) ? 3 : 2;
+      const int64_t cap = (int64_t)sms * CT;
+      const int grid = (int)(chunks < cap ? chunks : cap);
       if (grid == 0) return 0;
-      adamw_kernel<Tab, PDT, GDT, SDT><<<grid, kThreads, 0, st>>>(
+      adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT><<<grid, kThreads, 0, st>>>(
           tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
       return (int)cudaGetLastError();
     });
@@ -178,13 +195,26 @@ extern "C" DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, in
   ddpb200_adamw_bias_corrections(beta1, beta2, step, bc);
   AdamScalars a;
   a.lr = (float)lr; a.beta1 = (float)beta1; a.beta2 = (float)beta2; a.eps = (float)eps;
-  a.weight_decay = (float)weight_decay; a.lr_wd_valid = (weight_decay != 0.0) ? 1.f : 0.f;
-  a.bc1 = bc[0]; a.bc2_sqrt = bc[1];
+  a.weight_decay = (float)weight_decay;
+  a.bc1 = bc[0]; a.bc2_sqrt = bc[1]; a.rcp_bc2_sqrt = 1.0f / bc[1];   // IEEE: correctly rounded
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-#define DDPB200_ADAMW_CASE(P, G, S)                                                       \
-  if (param_dtype == P && grad_dtype == G && state_dtype == S)                            \
-    return launch_adamw<P, G, S>(table, table_loc, n, total_chunks, chunk_elems, a, lr_ptr, \
-                                 clip_coef, grad_scale, found_inf, flags, st);
+  // common cases get compile-time options; anything else takes the general kernel
+  int mode = kModeGeneral;
+  const bool plain = !grad_scale && a.weight_decay != 0.f &&
+                     !(flags & (DDPB200_ADAMW_MAXIMIZE | DDPB200_ADAMW_STORE_GRAD));
+  if (plain && clip_coef && (flags & DDPB200_ADAMW_ROUND_CLIPPED_GRAD)) mode = kModeFastClip;
+  else if (plain && !clip_coef) mode = kModeFastPlain;
+#define DDPB200_ADAMW_CASE(P, G, S)                                                                   \
+  if (param_dtype == P && grad_dtype == G && state_dtype == S) {                                      \
+    if (mode == kModeFastClip)                                                                        \
+      return launch_adamw<P, G, S, kModeFastClip>(table, table_loc, n, total_chunks, chunk_elems, a,  \
+                                                  lr_ptr, clip_coef, grad_scale, found_inf, flags, st); \
+    if (mode == kModeFastPlain)                                                                       \
+      return launch_adamw<P, G, S, kModeFastPlain>(table, table_loc, n, total_chunks, chunk_elems, a, \
+                                                   lr_ptr, clip_coef, grad_scale, found_inf, flags, st); \
+    return launch_adamw<P, G, S, kModeGeneral>(table, table_loc, n, total_chunks, chunk_elems, a,     \
+                                               lr_ptr, clip_coef, grad_scale, found_inf, flags, st);  \
+  }
   DDPB200_ADAMW_CASE(DDPB200_F32, DDPB200_F32, DDPB200_F32)
   DDPB200_ADAMW_CASE(DDPB200_BF16, DDPB200_BF16, DDPB200_BF16)
   DDPB200_ADAMW_CASE(DDPB200_BF16, DDPB200_BF16, DDPB200_F32)

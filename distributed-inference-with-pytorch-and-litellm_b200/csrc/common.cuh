@@ -13,8 +13,8 @@
 namespace ddpb200 {
 
 constexpr int kThreads   = 256;   // threads per CTA
-constexpr int kTileElems = 2048;  // elements one CTA moves per inner iteration (8 per thread)
-constexpr int kCtasPerSm = 4;     // persistent grid = SMs * kCtasPerSm
+constexpr int kTileElems = 2048;  // granularity of chunk sizes (elements)
+constexpr int kCtasPerSm = 3;     // persistent grid = SMs * kCtasPerSm (measured: 2-4 is the plateau, 8 loses 15 %)
 constexpr int kMaxValSegs = 448;  // segments that fit a by-value (launch-parameter) table
 
 // ---- segment tables ---------------------------------------------------------------
@@ -69,54 +69,118 @@ template <int DT> __device__ __forceinline__ float round_through(float x) {
 }
 
 // ---- vector groups -------------------------------------------------------------------
-// A "group" is G contiguous elements owned by one thread; G is chosen per kernel so that the
-// widest stream moves 16 bytes per request (G=4 if any fp32 stream is present, else 8).
-// Streaming cache policy: every byte is touched once per launch, so loads and stores carry
-// the evict-first (.cs) hint and do not displace each other's lines in L2.
+// A "group" is G contiguous elements owned by one thread. sm_100a has 256-bit global loads and
+// stores (LDG.E.256 / STG.E.256), which is also the only width that takes an L2 eviction hint:
+// every byte here is touched once per launch, so loads and stores are marked no-allocate in L1
+// and evict-first in L2 and do not displace each other's lines. A kernel picks G from the widest
+// stream (32 bytes of it per group); narrower streams of the same group use 128-bit accesses.
+// Pointers in the segment tables are generic; they are converted to the global window once.
+template <int W> struct Raw { uint32_t r[W]; };   // W 32-bit words
+
+__device__ __forceinline__ Raw<8> ldg256(const void* p) {
+  Raw<8> x;
+  asm volatile("ld.global.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]), "=r"(x.r[4]), "=r"(x.r[5]),
+                 "=r"(x.r[6]), "=r"(x.r[7]) : "l"(__cvta_generic_to_global(p)));
+  return x;
+}
+__device__ __forceinline__ void stg256(void* p, const Raw<8>& x) {
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               :: "l"(__cvta_generic_to_global(p)), "r"(x.r[0]), "r"(x.r[1]), "r"(x.r[2]), "r"(x.r[3]),
+                  "r"(x.r[4]), "r"(x.r[5]), "r"(x.r[6]), "r"(x.r[7]) : "memory");
+}
+__device__ __forceinline__ Raw<4> ldg128(const void* p) {
+  Raw<4> x;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]) : "l"(__cvta_generic_to_global(p)));
+  return x;
+}
+__device__ __forceinline__ void stg128(void* p, const Raw<4>& x) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+               :: "l"(__cvta_generic_to_global(p)), "r"(x.r[0]), "r"(x.r[1]), "r"(x.r[2]), "r"(x.r[3]) : "memory");
+}
+__device__ __forceinline__ Raw<2> ldg64(const void* p) {
+  Raw<2> x;
+  asm volatile("ld.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];"
+               : "=r"(x.r[0]), "=r"(x.r[1]) : "l"(__cvta_generic_to_global(p)));
+  return x;
+}
+__device__ __forceinline__ void stg64(void* p, const Raw<2>& x) {
+  asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};"
+               :: "l"(__cvta_generic_to_global(p)), "r"(x.r[0]), "r"(x.r[1]) : "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {   // a -> low half
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+// GroupIO<DT, G>: load G elements at element index i of a stream into fp32 registers / store back.
 template <int DT, int G> struct GroupIO;
 
-template <> struct GroupIO<DDPB200_F32, 4> {
-  static __device__ __forceinline__ void load(const void* p, int64_t i, float (&v)[4]) {
-    float4 t = __ldcs(reinterpret_cast<const float4*>(static_cast<const float*>(p) + i));
-    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-  }
-  static __device__ __forceinline__ void store(void* p, int64_t i, const float (&v)[4]) {
-    __stcs(reinterpret_cast<float4*>(static_cast<float*>(p) + i), make_float4(v[0], v[1], v[2], v[3]));
-  }
-};
-
-template <> struct GroupIO<DDPB200_BF16, 8> {
+template <> struct GroupIO<DDPB200_F32, 8> {
   static __device__ __forceinline__ void load(const void* p, int64_t i, float (&v)[8]) {
-    uint4 t = __ldcs(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p) + i));
-    v[0] = bf16_bits_to_f32(t.x & 0xffffu); v[1] = __uint_as_float(t.x & 0xffff0000u);
-    v[2] = bf16_bits_to_f32(t.y & 0xffffu); v[3] = __uint_as_float(t.y & 0xffff0000u);
-    v[4] = bf16_bits_to_f32(t.z & 0xffffu); v[5] = __uint_as_float(t.z & 0xffff0000u);
-    v[6] = bf16_bits_to_f32(t.w & 0xffffu); v[7] = __uint_as_float(t.w & 0xffff0000u);
+    Raw<8> t = ldg256(static_cast<const float*>(p) + i);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(t.r[k]);
   }
   static __device__ __forceinline__ void store(void* p, int64_t i, const float (&v)[8]) {
-    uint4 t;
-    __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]);
-    __nv_bfloat162 b = __floats2bfloat162_rn(v[2], v[3]);
-    __nv_bfloat162 c = __floats2bfloat162_rn(v[4], v[5]);
-    __nv_bfloat162 d = __floats2bfloat162_rn(v[6], v[7]);
-    t.x = *reinterpret_cast<uint32_t*>(&a); t.y = *reinterpret_cast<uint32_t*>(&b);
-    t.z = *reinterpret_cast<uint32_t*>(&c); t.w = *reinterpret_cast<uint32_t*>(&d);
-    __stcs(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p) + i), t);
+    Raw<8> t;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t.r[k] = __float_as_uint(v[k]);
+    stg256(static_cast<float*>(p) + i, t);
   }
 };
-
-template <> struct GroupIO<DDPB200_BF16, 4> {  // bf16 stream beside an fp32 one: 8-byte requests
+template <> struct GroupIO<DDPB200_F32, 4> {
   static __device__ __forceinline__ void load(const void* p, int64_t i, float (&v)[4]) {
-    uint2 t = __ldcs(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p) + i));
-    v[0] = bf16_bits_to_f32(t.x & 0xffffu); v[1] = __uint_as_float(t.x & 0xffff0000u);
-    v[2] = bf16_bits_to_f32(t.y & 0xffffu); v[3] = __uint_as_float(t.y & 0xffff0000u);
+    Raw<4> t = ldg128(static_cast<const float*>(p) + i);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = __uint_as_float(t.r[k]);
   }
   static __device__ __forceinline__ void store(void* p, int64_t i, const float (&v)[4]) {
-    uint2 t;
-    __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]);
-    __nv_bfloat162 b = __floats2bfloat162_rn(v[2], v[3]);
-    t.x = *reinterpret_cast<uint32_t*>(&a); t.y = *reinterpret_cast<uint32_t*>(&b);
-    __stcs(reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p) + i), t);
+    Raw<4> t;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) t.r[k] = __float_as_uint(v[k]);
+    stg128(static_cast<float*>(p) + i, t);
+  }
+};
+template <> struct GroupIO<DDPB200_BF16, 16> {
+  static __device__ __forceinline__ void load(const void* p, int64_t i, float (&v)[16]) {
+    Raw<8> t = ldg256(static_cast<const __nv_bfloat16*>(p) + i);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { v[2 * k] = bf16_bits_to_f32(t.r[k] & 0xffffu); v[2 * k + 1] = __uint_as_float(t.r[k] & 0xffff0000u); }
+  }
+  static __device__ __forceinline__ void store(void* p, int64_t i, const float (&v)[16]) {
+    Raw<8> t;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t.r[k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+    stg256(static_cast<__nv_bfloat16*>(p) + i, t);
+  }
+};
+template <> struct GroupIO<DDPB200_BF16, 8> {
+  static __device__ __forceinline__ void load(const void* p, int64_t i, float (&v)[8]) {
+    Raw<4> t = ldg128(static_cast<const __nv_bfloat16*>(p) + i);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { v[2 * k] = bf16_bits_to_f32(t.r[k] & 0xffffu); v[2 * k + 1] = __uint_as_float(t.r[k] & 0xffff0000u); }
+  }
+  static __device__ __forceinline__ void store(void* p, int64_t i, const float (&v)[8]) {
+    Raw<4> t;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) t.r[k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+    stg128(static_cast<__nv_bfloat16*>(p) + i, t);
+  }
+};
+template <> struct GroupIO<DDPB200_BF16, 4> {
+  static __device__ __forceinline__ void load(const void* p, int64_t i, float (&v)[4]) {
+    Raw<2> t = ldg64(static_cast<const __nv_bfloat16*>(p) + i);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) { v[2 * k] = bf16_bits_to_f32(t.r[k] & 0xffffu); v[2 * k + 1] = __uint_as_float(t.r[k] & 0xffff0000u); }
+  }
+  static __device__ __forceinline__ void store(void* p, int64_t i, const float (&v)[4]) {
+    Raw<2> t;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) t.r[k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+    stg64(static_cast<__nv_bfloat16*>(p) + i, t);
   }
 };
 
@@ -132,6 +196,21 @@ template <int DT> __device__ __forceinline__ void store1(void* p, int64_t i, flo
 
 template <int DT, int G> __device__ __forceinline__ bool group_aligned(const void* p) {
   return (reinterpret_cast<uintptr_t>(p) % (G * ElemOf<DT>::size)) == 0;
+}
+
+// Elements per group when the widest stream moves VECB bytes per access (VECB = 32 or 16).
+template <int VECB, bool ANY_F32> struct GroupSize { static constexpr int G = VECB / (ANY_F32 ? 4 : 2); };
+
+// x / c with IEEE round-to-nearest, for a divisor that is constant over the launch: reciprocal,
+// residual, correction (Markstein). rc must be the correctly rounded 1/c. Bit-identical to
+// __fdiv_rn(x, c) for finite normal quotients (checked exhaustively over all 2^23 significands for
+// 492 bias-correction constants in tests/test_oracle_golden.py::test_division_by_constant); the
+// select keeps x = +inf -> +inf. 3 issue slots instead of ~10.
+__device__ __forceinline__ float div_by_const(float x, float c, float rc) {
+  const float q0 = __fmul_rn(x, rc);
+  const float r = __fmaf_rn(-q0, c, x);
+  const float q = __fmaf_rn(r, rc, q0);
+  return (fabsf(q0) == __int_as_float(0x7f800000)) ? q0 : q;
 }
 
 // ---- reductions ------------------------------------------------------------------------

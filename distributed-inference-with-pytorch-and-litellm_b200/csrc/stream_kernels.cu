@@ -2,7 +2,7 @@
 //
 // One persistent launch covers every segment of a bucket (or of the whole model). A CTA
 // takes chunk c, c+grid, c+2*grid, ...; a chunk is a contiguous run of one segment, so every
-// warp request is a fully coalesced 512-byte (fp32) / 512-byte (bf16) line set. Roofline: HBM.
+// warp request is a fully coalesced run of 1 KB (256-bit accesses) or 512 B. Roofline: HBM.
 //   pack/unpack : s_src + s_dst bytes per element
 //   norm        : s bytes per element (read only)
 // The sum of squares, when asked for, is reduced warp-shuffle -> shared-memory tree -> one
@@ -11,10 +11,28 @@
 
 namespace ddpb200 {
 
-template <int SDT, int DDT> struct StreamGroup {
-  static constexpr int G = (SDT == DDPB200_F32 || DDT == DDPB200_F32) ? 4 : 8;
-  static constexpr int U = 8 / G;  // groups per thread per tile
-};
+// One chunk through G-element groups; returns the number of elements done (the ragged end is
+// left to the caller's scalar loop). NORM accumulates the squares of the values as stored.
+template <int SDT, int DDT, bool STORE, bool NORM, int VECB>
+__device__ __forceinline__ int64_t stream_chunk_vec(const char* src, char* dst, int64_t len, float scale,
+                                                    float& acc) {
+  constexpr bool any_f32 = (SDT == DDPB200_F32 || (STORE && DDT == DDPB200_F32));
+  constexpr int G = GroupSize<VECB, any_f32>::G;
+  const int64_t groups_end = len / G * G;
+#pragma unroll 2
+  for (int64_t i = (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
+    float x[G];
+    GroupIO<SDT, G>::load(src, i, x);
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      float y = __fmul_rn(x[k], scale);
+      if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+      x[k] = y;
+    }
+    if constexpr (STORE) GroupIO<DDT, G>::store(dst, i, x);
+  }
+  return groups_end;
+}
 
 // SRC / DST: which ptr[] slot is read / written. STORE=false -> norm only.
 template <class Tab, int SDT, int DDT, int SRC, int DST, bool STORE, bool NORM, bool DEVSCALE>
@@ -22,8 +40,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
               float scale, const float* __restrict__ scale_ptr, float* __restrict__ sumsq_out,
               float* __restrict__ chunk_partials, uint32_t* ticket) {
-  constexpr int G = StreamGroup<SDT, DDT>::G;
-  constexpr int U = StreamGroup<SDT, DDT>::U;
+  constexpr bool any_f32 = (SDT == DDPB200_F32 || (STORE && DDT == DDPB200_F32));
+  constexpr int G32 = GroupSize<32, any_f32>::G, G16 = GroupSize<16, any_f32>::G;
   __shared__ float red[kThreads / 32];
 
   if constexpr (DEVSCALE) scale = __ldg(scale_ptr);
@@ -39,53 +57,16 @@ stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chu
     if constexpr (STORE) dst = static_cast<char*>(tab.ptr(s, DST)) + start * ElemOf<DDT>::size;
 
     float acc = 0.f;
-    bool vec = group_aligned<SDT, G>(src);
-    if constexpr (STORE) vec = vec && group_aligned<DDT, G>(dst);
-
-    if (vec) {
-      const int64_t full = len / kTileElems * kTileElems;
-      for (int64_t t0 = 0; t0 < full; t0 += kTileElems) {
-        float x[U][G];
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-          GroupIO<SDT, G>::load(src, t0 + u * (kThreads * G) + threadIdx.x * G, x[u]);
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-#pragma unroll
-          for (int k = 0; k < G; ++k) {
-            float y = __fmul_rn(x[u][k], scale);
-            if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
-            x[u][k] = y;
-          }
-          if constexpr (STORE)
-            GroupIO<DDT, G>::store(dst, t0 + u * (kThreads * G) + threadIdx.x * G, x[u]);
-        }
-      }
-      // ragged end of the chunk: whole groups, then single elements
-      const int64_t groups_end = len / G * G;
-      for (int64_t i = full + (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
-        float x[G];
-        GroupIO<SDT, G>::load(src, i, x);
-#pragma unroll
-        for (int k = 0; k < G; ++k) {
-          float y = __fmul_rn(x[k], scale);
-          if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
-          x[k] = y;
-        }
-        if constexpr (STORE) GroupIO<DDT, G>::store(dst, i, x);
-      }
-      for (int64_t i = groups_end + threadIdx.x; i < len; i += kThreads) {
-        float y = __fmul_rn(load1<SDT>(src, i), scale);
-        if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
-        if constexpr (STORE) store1<DDT>(dst, i, y);
-      }
-    } else {
-      // a segment whose base is not 16-byte aligned (odd element offset inside a bucket)
-      for (int64_t i = threadIdx.x; i < len; i += kThreads) {
-        float y = __fmul_rn(load1<SDT>(src, i), scale);
-        if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
-        if constexpr (STORE) store1<DDT>(dst, i, y);
-      }
+    bool a32 = group_aligned<SDT, G32>(src), a16 = group_aligned<SDT, G16>(src);
+    if constexpr (STORE) { a32 = a32 && group_aligned<DDT, G32>(dst); a16 = a16 && group_aligned<DDT, G16>(dst); }
+    int64_t done = 0;
+    if (a32) done = stream_chunk_vec<SDT, DDT, STORE, NORM, 32>(src, dst, len, scale, acc);
+    else if (a16) done = stream_chunk_vec<SDT, DDT, STORE, NORM, 16>(src, dst, len, scale, acc);
+    // ragged end, or a segment whose base is not 16-byte aligned (odd element offset inside a bucket)
+    for (int64_t i = done + threadIdx.x; i < len; i += kThreads) {
+      float y = __fmul_rn(load1<SDT>(src, i), scale);
+      if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+      if constexpr (STORE) store1<DDT>(dst, i, y);
     }
 
     if constexpr (NORM) {

@@ -56,6 +56,8 @@ def lib() -> ctypes.CDLL:
         L.oracle_single_tensor_adamw.restype = None
         L.oracle_single_tensor_adamw.argtypes = [vp, i32, vp, i32, vp, vp, i32, i64, f64, f64, f64,
                                                  f64, f64, i64]
+        L.oracle_div_by_const_mismatches.restype = i64
+        L.oracle_div_by_const_mismatches.argtypes = [f32]
         _lib = L
     return _lib
 
@@ -158,3 +160,8 @@ def fused_clip_adamw(p, g, m, v, *, lr, beta1, beta2, eps, weight_decay, step, c
 def single_tensor_adamw(p, g, m, v, *, lr, beta1, beta2, eps, weight_decay, step) -> None:
     lib().oracle_single_tensor_adamw(_p(p), _dt(p), _p(g), _dt(g), _p(m), _p(v), _dt(m), p.size,
                                      lr, beta1, beta2, eps, weight_decay, step)
+
+
+def div_by_const_mismatches(c: float) -> int:
+    """How many of the 2^23 significands x give fma-sequence(x, c) != x / c (see ddp_oracle.c)."""
+    return int(lib().oracle_div_by_const_mismatches(np.float32(c)))

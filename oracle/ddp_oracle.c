@@ -247,3 +247,24 @@ void oracle_single_tensor_adamw(void* p, int p_dt, const void* g, int g_dt, void
     st(p, i, p_dt, pi); st(m, i, s_dt, mi); st(v, i, s_dt, vi);
   }
 }
+
+/* ---- check of the kernel's division by a per-launch constant -----------------------------------
+ * csrc/common.cuh div_by_const computes x / c as q0 = x*rc; r = fma(-q0, c, x); q = fma(r, rc, q0)
+ * with rc = RN(1/c). This counts, over ALL 2^23 significands of x in [1, 2), how often that differs
+ * from the IEEE quotient x / c (scaling x by a power of two scales every step exactly). The oracle's
+ * own AdamW above uses the plain '/' operator; this function exists so a CPU test can show that the
+ * two are the same function for the constants the kernel meets. */
+int64_t oracle_div_by_const_mismatches(float c) {
+  const float rc = 1.0f / c;
+  int64_t bad = 0;
+  for (uint32_t mant = 0; mant < (1u << 23); ++mant) {
+    const uint32_t u = 0x3f800000u | mant;
+    float x;
+    memcpy(&x, &u, 4);
+    const float q0 = x * rc;
+    const float r = fmaf(-q0, c, x);
+    const float q = fmaf(r, rc, q0);
+    if (q != x / c) ++bad;
+  }
+  return bad;
+}
