@@ -19,6 +19,7 @@ TABLE_HOST, TABLE_DEVICE = 0, 1
 NORM_EXACT_F32, NORM_TORCH_BF16 = 0, 1
 ADAMW_ROUND_CLIPPED_GRAD, ADAMW_STORE_GRAD, ADAMW_MAXIMIZE = 1, 2, 4
 TILE_ELEMS = 2048
+STATIC_SCRATCH_MAX_CHUNKS = 262144
 
 
 class Seg(ctypes.Structure):
@@ -42,6 +43,7 @@ SIGNATURES = {
     "ddpb200_suggest_chunk_elems": (_i64, [_i64, _i32]),
     "ddpb200_pack_scale_cast": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _f32, _vp, _vp, _vp, _vp]),
     "ddpb200_l2norm_sumsq": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp]),
+    "ddpb200_l2norm_sumsq_static": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _vp, _vp]),
     "ddpb200_l2norm_finalize": (ctypes.c_int, [_vp, _i64, _i32, _f32, _vp, _vp]),
     "ddpb200_scale_by_device_scalar": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _vp, _vp]),
     "ddpb200_fused_clip_adamw": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _f64, _vp,

@@ -7,6 +7,7 @@
 //   norm        : s bytes per element (read only)
 // The sum of squares, when asked for, is reduced warp-shuffle -> shared-memory tree -> one
 // float per chunk -> "last CTA" fold per segment (common.cuh), i.e. single pass, one launch.
+#include <mutex>
 #include "launch.cuh"
 
 namespace ddpb200 {
@@ -205,4 +206,65 @@ extern "C" DDPB200_API int ddpb200_l2norm_finalize(const float* sumsq, int64_t n
   if (mode != DDPB200_NORM_EXACT_F32 && mode != DDPB200_NORM_TORCH_BF16) return DDPB200_E_INVALID;
   norm_finalize_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(sumsq, n, mode, max_norm, out);
   return (int)cudaGetLastError();
+}
+
+// ---- L2 norm for callers that cannot bring scratch memory ------------------------------------------
+// Same kernel as ddpb200_l2norm_sumsq; the per-chunk partial sums and the ticket counter live in a
+// fixed array that is part of this library's device image instead of in caller memory.
+
+namespace ddpb200 {
+
+constexpr int64_t kStaticTicketBytes = 256;   // the ticket sits alone in the first 256 bytes
+constexpr int64_t kStaticScratchBytes = kStaticTicketBytes + (int64_t)DDPB200_STATIC_SCRATCH_MAX_CHUNKS * sizeof(float);
+
+// One copy per GPU that loads the library, resident until the process exits (1 MiB + 256 B).
+static __device__ __align__(256) unsigned char g_norm_scratch[kStaticScratchBytes];
+
+// In host code `g_norm_scratch` is only a handle for the runtime, not a device address: the
+// address has to be asked for, per device, with that device current.
+static std::mutex g_scratch_mutex;
+static void* g_scratch_addr[64] = {nullptr};
+
+static int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return DDPB200_E_INVALID;
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
+  if (!g_scratch_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_norm_scratch);      // first call on this device: set-up
+    if (e != cudaSuccess) return (int)e;
+    if (!p) return DDPB200_E_INVALID;
+    g_scratch_addr[dev] = p;
+  }
+  *out = g_scratch_addr[dev];
+  return 0;
+}
+
+}  // namespace ddpb200
+
+extern "C" DDPB200_API int ddpb200_l2norm_sumsq_static(const ddpb200_seg* table, int32_t table_loc,
+                                                       int64_t n, int64_t total_chunks,
+                                                       int64_t chunk_elems, int32_t dtype,
+                                                       float* sumsq_out, void* stream) {
+  if (total_chunks > DDPB200_STATIC_SCRATCH_MAX_CHUNKS) return DDPB200_E_TOO_LARGE;
+  void* base = nullptr;
+  const int rc = static_scratch_for_current_device(&base);
+  if (rc != 0) return rc;
+  uint32_t* ticket = static_cast<uint32_t*>(base);
+  float* partials = reinterpret_cast<float*>(static_cast<unsigned char*>(base) + kStaticTicketBytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array keeps whatever the previous call left in it. The partials are fully rewritten before
+  // they are read; the ticket is the one thing that must start at zero, so it is cleared here, on
+  // the caller's stream, rather than trusted.
+  cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(uint32_t), st);
+  if (e != cudaSuccess) return (int)e;
+  if (dtype == DDPB200_F32)
+    return launch_stream<DDPB200_F32, DDPB200_F32, 1, 1, false, true, false>(
+        table, table_loc, n, total_chunks, chunk_elems, 1.0f, nullptr, sumsq_out, partials, ticket, st);
+  if (dtype == DDPB200_BF16)
+    return launch_stream<DDPB200_BF16, DDPB200_BF16, 1, 1, false, true, false>(
+        table, table_loc, n, total_chunks, chunk_elems, 1.0f, nullptr, sumsq_out, partials, ticket, st);
+  return DDPB200_E_UNSUPPORTED;
 }

@@ -134,6 +134,30 @@ DDPB200_API int ddpb200_l2norm_sumsq(const ddpb200_seg* table, int32_t table_loc
                          int64_t chunk_elems, int32_t dtype, float* sumsq_out,
                          float* chunk_partials, uint32_t* ticket, void* stream);
 
+/* Same result as ddpb200_l2norm_sumsq for a caller that has no scratch memory to give and no way
+ * to get any. (No counterpart in the reference or in torch: an addition of this library.)
+ * Who that is: a host binding that only ever sees its own input and output buffers (a cgo / JNI /
+ * ctypes caller without a device allocator behind it); a caller inside a region where device
+ * allocation is off limits because cudaMalloc synchronises the whole device (the inner loop of a
+ * latency-critical step); a process whose device memory has all been handed to a pool that the
+ * call site cannot reach.
+ * The per-chunk partial sums and the ticket counter live in an array built into the library
+ * image: DDPB200_STATIC_SCRATCH_MAX_CHUNKS floats + 256 bytes = 1 MiB + 256 B on every GPU that
+ * loads the library, held until the process exits. total_chunks beyond that limit is refused with
+ * DDPB200_E_TOO_LARGE ("size exceeds the stated limit"): use a larger chunk_elems, or the entry
+ * point above with your own scratch. The function calls no cudaMalloc/cudaFree and nothing that
+ * allocates; inputs (table, ptr[1] = grad) and the output sumsq_out[n] are still the caller's.
+ * The first call on each device looks the array's address up (cudaGetSymbolAddress, with that
+ * device current) and keeps it; make that first call before any stream capture begins.
+ * ALL calls on a device share the one array: two calls whose kernels can overlap on the GPU
+ * (different streams without an ordering between them) race on it and give wrong sums. Calls on
+ * one stream, or ordered by events, are safe. The array keeps the previous call's contents; the
+ * ticket is cleared at the start of every call, the partials are overwritten before use. */
+#define DDPB200_STATIC_SCRATCH_MAX_CHUNKS 262144
+DDPB200_API int ddpb200_l2norm_sumsq_static(const ddpb200_seg* table, int32_t table_loc, int64_t n,
+                                            int64_t total_chunks, int64_t chunk_elems, int32_t dtype,
+                                            float* sumsq_out, void* stream);
+
 /* total norm + clip coefficient, on device, no host sync
  * (TORCH/nn/utils/clip_grad.py:106-108,165,169). out[0] = total norm (pre-clip),
  * out[1] = min(max_norm/(total+1e-6), 1). mode = DDPB200_NORM_*. */
