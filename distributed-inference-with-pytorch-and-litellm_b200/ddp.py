@@ -66,11 +66,15 @@ class GradBucket:
 
 
 class _Bucket:
-    __slots__ = ("index", "spec", "buffer", "views", "first", "pending", "future", "work", "dtype")
+    __slots__ = ("index", "spec", "buffer", "views", "first", "n", "params", "sumsq", "pending", "future",
+                 "work", "dtype")
 
-    def __init__(self, index, spec, buffer, views, first):
+    def __init__(self, index, spec, buffer, views, first, params):
         self.index, self.spec, self.buffer, self.views, self.first = index, spec, buffer, views, first
-        self.pending = len(spec.indices)
+        self.n = len(spec.indices)
+        self.params = params            # the bucket's parameters, bucket order
+        self.sumsq = None               # this bucket's slice of the per-tensor sum-of-squares array
+        self.pending = self.n
         self.future = None
         self.work = None
         self.dtype = buffer.dtype
@@ -98,6 +102,7 @@ class DistributedDataParallel(nn.Module):
         self.require_backward_grad_sync = True
         self.process_group = process_group if process_group is not None else dist.group.WORLD
         self.world_size = dist.get_world_size(self.process_group)
+        self._inv_world_size = float(np.float32(1.0 / self.world_size))     # float(1.0/ws), as div_factor_
         self.rank = dist.get_rank(self.process_group)
         self.parameters_to_ignore = set(getattr(module, "_ddp_params_and_buffers_to_ignore", []))
 
@@ -228,7 +233,7 @@ class DistributedDataParallel(nn.Module):
             dt = self._params[spec.indices[0]].dtype
             buf = torch.zeros(spec.numel, dtype=dt, device=self.device)
             views = [buf[o:o + numels[i]].view_as(self._params[i]) for i, o in zip(spec.indices, spec.offsets)]
-            self._buckets.append(_Bucket(b, spec, buf, views, first))
+            self._buckets.append(_Bucket(b, spec, buf, views, first, [self._params[i] for i in spec.indices]))
             self._order.extend(spec.indices)
             first += len(spec.indices)
         n = len(self._order)
@@ -245,6 +250,8 @@ class DistributedDataParallel(nn.Module):
         self._view_table = k.table([None, all_views, None, None], onum, chunk_elems=self._pack_table.chunk_elems,
                                    device=self.device if self._cuda else None)
         self._sumsq = torch.zeros(n, dtype=torch.float32, device=self.device)
+        for bk in self._buckets:
+            bk.sumsq = self._sumsq[bk.first:bk.first + bk.n]
         self._norm_out = torch.zeros(2, dtype=torch.float32, device=self.device)
         self._sumsq_valid = False
         self._next_bucket = 0
@@ -369,42 +376,40 @@ class DistributedDataParallel(nn.Module):
 
     def _launch_bucket(self, bk: _Bucket) -> None:
         k = self._kernels
-        n = len(bk.spec.indices)
+        n, first = bk.n, bk.first
         grads = []
-        for pi, view in zip(bk.spec.indices, bk.views):
-            g = self._params[pi].grad
+        for p in bk.params:
+            g = p.grad
             if g is None:
                 raise RuntimeError("ddp_b200: gradient missing for a parameter marked ready")
             if not g.is_contiguous():
                 g = g.contiguous()
-                self._params[pi].grad = g
+                p.grad = g
             grads.append(g)
         gdt = grads[0].dtype
-        if any(g.dtype != gdt for g in grads):
-            raise RuntimeError("ddp_b200: gradients of one bucket must share a dtype")
-        self._pack_table.host["ptr"][bk.first:bk.first + n, 0] = np.fromiter(
-            (g.data_ptr() for g in grads), dtype=np.uint64, count=n)
+        for g in grads:
+            if g.dtype != gdt:
+                raise RuntimeError("ddp_b200: gradients of one bucket must share a dtype")
+        self._pack_table.host["ptr"][first:first + n, 0] = [g.data_ptr() for g in grads]
         hooked = self._comm_hook is not None
         # no hook: pre-divide, then SUM (div_factor_, reducer.hpp:497-500). With a hook the hook divides.
-        scale = 1.0 if hooked else float(np.float32(1.0 / self.world_size))
+        scale = 1.0 if hooked else self._inv_world_size
         local_only = self.world_size == 1 and not hooked
-        sumsq_slice = self._sumsq[bk.first:bk.first + n]
         if local_only and not self.gradient_as_bucket_view:
             # world_size 1, grads stay where autograd put them: nothing to exchange or copy, only the
             # norm pass is left (ptr[1] = grad)
-            self._unpack_table.host["ptr"][bk.first:bk.first + n, 1] = self._pack_table.host["ptr"][bk.first:bk.first + n, 0]
-            k.sumsq(self._unpack_table, gdt, sumsq_slice, first=bk.first, count=n, prefer_device=False)
+            self._unpack_table.host["ptr"][first:first + n, 1] = self._pack_table.host["ptr"][first:first + n, 0]
+            k.sumsq(self._unpack_table, gdt, bk.sumsq, first=first, count=n, prefer_device=False)
             self._stats["norm_launches"] += 1
             return
         # world_size 1 with bucket views: the norm rides on the pack pass
-        k.pack(self._pack_table, gdt, bk.dtype, scale, first=bk.first, count=n,
-               sumsq_out=sumsq_slice if local_only else None, prefer_device=False)
+        k.pack(self._pack_table, gdt, bk.dtype, scale, first=first, count=n,
+               sumsq_out=bk.sumsq if local_only else None, prefer_device=False)
         self._stats["pack_launches"] += 1
         if local_only:
             return
         if hooked:
-            gb = GradBucket(bk.index, bk.buffer, list(bk.views), [self._params[i] for i in bk.spec.indices],
-                            bk.index == len(self._buckets) - 1)
+            gb = GradBucket(bk.index, bk.buffer, list(bk.views), list(bk.params), bk.index == len(self._buckets) - 1)
             bk.future = self._comm_hook(self._comm_hook_state, gb)
             self._stats["allreduces"] += 1
             return
@@ -426,16 +431,15 @@ class DistributedDataParallel(nn.Module):
         gradients, and (unless grads are bucket views) the copy back into p.grad
         (finalize_bucket_dense / copy_bucket_to_grad, reducer.hpp:328-334)."""
         k = self._kernels
-        n = len(bk.spec.indices)
+        n = bk.n
         if self.gradient_as_bucket_view:
-            k.sumsq(self._view_table, bk.dtype, self._sumsq[bk.first:bk.first + n], first=bk.first, count=n)
+            k.sumsq(self._view_table, bk.dtype, bk.sumsq, first=bk.first, count=n)
             self._stats["norm_launches"] += 1
         else:
-            self._unpack_table.host["ptr"][bk.first:bk.first + n, 1] = np.fromiter(
-                (g.data_ptr() for g in grads), dtype=np.uint64, count=n)
+            self._unpack_table.host["ptr"][bk.first:bk.first + n, 1] = [g.data_ptr() for g in grads]
             # unpack and norm in one pass over the bucket
             k.pack(self._unpack_table, bk.dtype, grads[0].dtype, 1.0, first=bk.first, count=n,
-                   sumsq_out=self._sumsq[bk.first:bk.first + n], prefer_device=False)
+                   sumsq_out=bk.sumsq, prefer_device=False)
             self._stats["unpack_launches"] += 1
 
     def _finalize_backward(self) -> None:
@@ -481,8 +485,15 @@ class DistributedDataParallel(nn.Module):
         if grads is not None:
             for p, g in zip(self._params, grads):
                 p.grad = g
-        for pi in (order if order is not None else self._order):
-            self._on_grad_ready(pi, False)
+        if order is None and self._has_rebuilt:
+            # every gradient is already there: walk the buckets in order, no per-parameter bookkeeping
+            for bk in self._buckets:
+                bk.pending = 0
+                self._launch_bucket(bk)
+            self._next_bucket = len(self._buckets)
+        else:
+            for pi in (order if order is not None else self._order):
+                self._on_grad_ready(pi, False)
         self._finalize_backward()
 
     def clip_grad_norm_(self, max_norm: float, norm_type: float = 2.0, error_if_nonfinite: bool = False,

@@ -42,6 +42,8 @@ class SegTable:
                  chunk_elems: Optional[int] = None):
         n = len(numels)
         self.n = n
+        self.dev: Optional[torch.Tensor] = None
+        self._args_cache = {}
         self.host = np.zeros(n, dtype=SEG_DTYPE)
         self.host["numel"] = np.asarray(numels, dtype=np.int64)
         for k, col in enumerate(cols):
@@ -57,26 +59,40 @@ class SegTable:
         self.host["chunk_begin"] = begins[:-1]
         self.chunk_begins = begins  # n+1 entries, for slicing
         self.total_chunks = int(begins[-1])
-        self.dev: Optional[torch.Tensor] = None
 
     def set_col(self, k: int, tensors: Sequence[torch.Tensor]) -> None:
         self.host["ptr"][:, k] = np.fromiter((t.data_ptr() for t in tensors), dtype=np.uint64, count=self.n)
-        self.dev = None
+        self.invalidate_device()
+
+    def invalidate_device(self) -> None:
+        if self.dev is not None:
+            self.dev = None
+            self._args_cache.clear()
 
     def col(self, k: int) -> np.ndarray:
         return self.host["ptr"][:, k]
 
     def to_device(self, device) -> "SegTable":
         self.dev = torch.from_numpy(self.host.view(np.uint8).copy()).to(device)
+        self._args_cache.clear()
         return self
 
-    # (pointer, location, n, total_chunks, first_seg, first_chunk) of rows [first, first+count)
+    # (pointer, location, n, total_chunks) of rows [first, first+count); cached: this sits on the
+    # per-bucket launch path and the answers never change while the table lives
     def args(self, first: int = 0, count: Optional[int] = None, prefer_device: bool = True):
-        count = self.n - first if count is None else count
-        chunks = int(self.chunk_begins[first + count] - self.chunk_begins[first])
-        if prefer_device and self.dev is not None:
-            return self.dev.data_ptr() + 48 * first, TABLE_DEVICE, count, chunks
-        return self.host.ctypes.data + 48 * first, TABLE_HOST, count, chunks
+        on_dev = prefer_device and self.dev is not None
+        key = (first, count, on_dev)
+        hit = self._args_cache.get(key)
+        if hit is not None:
+            return hit
+        cnt = self.n - first if count is None else count
+        chunks = int(self.chunk_begins[first + cnt] - self.chunk_begins[first])
+        if on_dev:
+            out = (self.dev.data_ptr() + 48 * first, TABLE_DEVICE, cnt, chunks)
+        else:
+            out = (self.host.ctypes.data + 48 * first, TABLE_HOST, cnt, chunks)
+        self._args_cache[key] = out
+        return out
 
 
 class _Workspace:

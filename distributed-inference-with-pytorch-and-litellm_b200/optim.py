@@ -53,6 +53,7 @@ class AdamW(Optimizer):
         self._state_dtype = state_dtype
         self._clip_coef: Optional[torch.Tensor] = None
         self._tables: Dict[Tuple, Tuple[np.ndarray, np.ndarray, SegTable]] = {}
+        self._plan: Dict[int, dict] = {}
         self.round_clipped_grad = True   # reproduce torch's rounding of g*coef to the grad dtype
         self.launches_last_step = 0
 
@@ -93,27 +94,47 @@ class AdamW(Optimizer):
 
         for gi, group in enumerate(self.param_groups):
             beta1, beta2 = group["betas"]
-            buckets: Dict[Tuple, List[torch.Tensor]] = {}
-            for p in group["params"]:
-                if p.grad is None:
-                    continue
-                if p.grad.is_sparse:
-                    raise RuntimeError("AdamW does not support sparse gradients")
-                if not (p.is_contiguous() and p.grad.is_contiguous()):
-                    raise RuntimeError("ddp_b200.AdamW needs contiguous parameters and gradients")
-                st = self._init_state(p)
-                st["step"] += 1
-                key = (p.device, p.dtype, p.grad.dtype, st["exp_avg"].dtype, int(st["step"]))
-                buckets.setdefault(key, []).append(p)
-            for key, plist in buckets.items():
-                device, pdt, gdt, sdt, step = key
-                tab = self._table_for((gi,) + key[:4], plist, device)
+            with_grad = [p for p in group["params"] if p.grad is not None]
+            if not with_grad:
+                continue
+            for li, launch in enumerate(self._partition(gi, with_grad)):
+                key, plist, steps = launch[0], launch[1], launch[2]
+                torch._foreach_add_(steps, 1.0)       # the per-parameter `step` scalars (CPU), one call
+                launch[3] += 1
+                device, pdt, gdt, sdt = key
+                tab = self._table_for((gi, li) + key, plist, device)
                 k.adamw(tab, pdt, gdt, sdt, lr=group["lr"], beta1=beta1, beta2=beta2, eps=group["eps"],
-                        weight_decay=group["weight_decay"], step=step, clip_coef=clip_coef,
+                        weight_decay=group["weight_decay"], step=launch[3], clip_coef=clip_coef,
                         grad_scale=grad_scale, found_inf=None, round_clipped=self.round_clipped_grad,
                         store_grad=grad_scale is not None, maximize=group["maximize"])
                 self.launches_last_step += 1
         return loss
+
+    def _partition(self, gi: int, with_grad: List[torch.Tensor]):
+        """Split the parameters that have a gradient into launches, one per (device, param dtype,
+        grad dtype, state dtype, step count): a list of [key, params, step tensors, step]. The split
+        is remembered; while the same parameters show up with the same gradient dtypes (every
+        ordinary training step) it is reused without touching per-parameter state again."""
+        ids = [id(p) for p in with_grad]
+        ent = self._plan.get(gi)
+        if ent is not None and ent[0] == ids and all(L[1][0].grad.dtype == L[0][2] for L in ent[1]):
+            return ent[1]
+        groups: Dict[Tuple, List[torch.Tensor]] = {}
+        for p in with_grad:
+            if p.grad.is_sparse:
+                raise RuntimeError("AdamW does not support sparse gradients")
+            if not (p.is_contiguous() and p.grad.is_contiguous()):
+                raise RuntimeError("ddp_b200.AdamW needs contiguous parameters and gradients")
+            st = self._init_state(p)
+            groups.setdefault((p.device, p.dtype, p.grad.dtype, st["exp_avg"].dtype, int(st["step"])), []).append(p)
+        launches = [[k5[:4], plist, [self.state[p]["step"] for p in plist], k5[4]] for k5, plist in groups.items()]
+        self._plan[gi] = (ids, launches)
+        return launches
+
+    def load_state_dict(self, state_dict) -> None:
+        super().load_state_dict(state_dict)
+        self._plan.clear()          # step counts and state tensors were replaced
+        self._tables.clear()
 
     def _table_for(self, key, plist: List[torch.Tensor], device) -> SegTable:
         """Segment table for this group. Parameter / state pointers never move; gradient pointers
@@ -130,7 +151,7 @@ class AdamW(Optimizer):
                     tab.to_device(device)     # second sighting of the same pointers: make it resident
                 return tab
             tab.host["ptr"][:, 1] = gptr
-            tab.dev = None
+            tab.invalidate_device()
             self._tables[key] = (pptr, gptr, tab)
             return tab
         states = [self.state[p] for p in plist]
