@@ -3,8 +3,9 @@
 
 A *step* is one pass of the hot path over one set of synthetic gradients for the Llama-3.2-1B
 architecture in bf16 (BASELINE.json configs[1]: 146 parameter tensors, 1,235,814,400 elements):
-per bucket pack (flatten + 1/world_size + cast) -> NCCL allreduce on a side stream (N>1) ->
-per-tensor sum of squares; then total norm + clip coefficient on the device; then ONE fused
+N>1: per bucket pack (flatten + 1/world_size + cast) -> NCCL allreduce on a side stream ->
+per-tensor sum of squares; N=1: nothing to exchange, so one coalesced sum-of-squares launch over the
+gradients where they lie. Then total norm + clip coefficient on the device; then ONE fused
 clip+AdamW launch over all parameters. Forward/backward of the model are not part of the path
 (SURVEY.md §8f-2 lists them as the next row).
 
@@ -256,24 +257,61 @@ def run_ours(args):
     allreduces = stats1["allreduces"] - stats0["allreduces"]
 
     # ---- timed: end to end from HOST gradients ---------------------------------------------------
-    # the gradients of the step arrive from pinned host memory (H2D inside the timed region), the
-    # result read back is the pre-clip total norm (D2H, then a host read).
+    # Each step's gradients arrive from pinned host memory (H2D inside the timed region) and the
+    # pre-clip total norm is read back on the host (D2H). The copies run bucket by bucket on a copy
+    # stream into one of two landing buffers, so a bucket is processed as soon as it has landed and
+    # the update of step k overlaps the transfer of step k+1.
     e2e_steps = max(2, min(args.steps, 10))
+    layout = ddp.bucket_layout()
+    order_now = [pi for b in layout for pi in b["parameters"]]
     host_g = torch.empty(total, dtype=dtype).pin_memory()
     host_g.copy_(gflat)
+    land = [gflat, torch.empty_like(gflat)]
+    land_views, bucket_span = [], []
+    for buf in land:                         # landing buffers are laid out in bucket order
+        views, o = [None] * len(params), 0
+        for pi in order_now:
+            views[pi] = buf[o:o + numel[pi]].view(shapes[pi])
+            o += numel[pi]
+        land_views.append(views)
+    o = 0
+    for b in layout:
+        bucket_span.append((o, o + b["numel"]))
+        o += b["numel"]
+    copy_stream = torch.cuda.Stream(device=dev)
+    landed = [[torch.cuda.Event() for _ in layout] for _ in land]
+    consumed = [torch.cuda.Event() for _ in land]
+    norm_ready = [torch.cuda.Event() for _ in land]
+    norm_host2 = [torch.empty(2, dtype=torch.float32).pin_memory() for _ in land]
+    for ev_ in consumed:
+        ev_.record()
+
+    def h2d(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])             # the buffer's previous reader is done
+            for b, (lo, hi) in enumerate(bucket_span):
+                land[slot][lo:hi].copy_(host_g[lo:hi], non_blocking=True)
+                landed[slot][b].record()
+
     sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     last_norm = 0.0
-    for _ in range(e2e_steps):
-        gflat.copy_(host_g, non_blocking=True)
-        ddp.reduce_gradients(grads)
+    h2d(0)
+    for it in range(e2e_steps):
+        slot = it % 2
+        if it + 1 < e2e_steps:
+            h2d(1 - slot)                                      # next step's gradients start moving now
+        cur = torch.cuda.current_stream()
+        ddp.reduce_gradients(land_views[slot], before_bucket=lambda b, _idx: cur.wait_event(landed[slot][b]))
         ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
-        norm_host.copy_(ddp._norm_out, non_blocking=True)
+        norm_host2[slot].copy_(ddp._norm_out, non_blocking=True)
+        norm_ready[slot].record()
         opt.step()
+        consumed[slot].record()
         opt.zero_grad()
-        torch.cuda.current_stream().synchronize()
-        last_norm = float(norm_host[0])
+        norm_ready[slot].synchronize()                         # the step's result, on the host
+        last_norm = float(norm_host2[slot][0])
     e1.record()
     sync_all()
     e2e_ms = e0.elapsed_time(e1)
@@ -303,15 +341,16 @@ def run_ours(args):
             "steps_per_s": args.steps / (ms * 1e-3),
             "e2e": {"value": ws * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "steps": e2e_steps,
                     "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8,
-                    "note": "gradients of each step copied from pinned host memory; total norm read back"},
+                    "note": "gradients of each step copied from pinned host memory (bucket by bucket, double "
+                            "buffered); total norm read back on the host every step"},
             "gpu_launches": launches,
             "nccl_allreduces": allreduces,
             "roofline": {"kernel": "adamw_kernel (fused clip+AdamW, bf16)", "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                          "frac_of_8000_nominal": achieved / 8000.0, "algorithmic_bytes_per_launch": alg_bytes,
                          "avg_launch_ms": adamw_ms, "traffic": adamw_traffic_from_profile()},
-            "path_bytes_per_step": {"pack": 4 * total, "norm": 0 if ws == 1 else 2 * total, "adamw": 14 * total},
-            "path_gbs": (4 * total + (0 if ws == 1 else 2 * total) + 14 * total) / (ms / args.steps * 1e-3) / 1e9,
+            "path_bytes_per_step": {"pack": 0 if ws == 1 else 4 * total, "norm": 2 * total, "adamw": 14 * total},
+            "path_gbs": ((0 if ws == 1 else 4 * total) + 2 * total + 14 * total) / (ms / args.steps * 1e-3) / 1e9,
             "clocks": clk, "total_norm": last_norm,
         }
         if ws > 1:

@@ -370,9 +370,63 @@ class DistributedDataParallel(nn.Module):
                                "(shared across multiple forward passes needs static_graph / no_sync)")
         # buckets are reduced strictly in sequence so every rank issues the same collectives in
         # the same order (mark_bucket_ready, reducer.hpp:282)
+        b0 = self._next_bucket
         while self._next_bucket < len(self._buckets) and self._buckets[self._next_bucket].pending == 0:
-            self._launch_bucket(self._buckets[self._next_bucket])
             self._next_bucket += 1
+        if self._next_bucket > b0:
+            self._launch_buckets(b0, self._next_bucket)
+
+    @property
+    def _local_only(self) -> bool:
+        """world_size 1 and no hook: there is nothing to exchange, so gradients stay where autograd
+        put them (no bucket copy, whatever gradient_as_bucket_view says) and only the norm pass is left."""
+        return self.world_size == 1 and self._comm_hook is None
+
+    def _launch_buckets(self, b0: int, b1: int) -> None:
+        """Buckets b0..b1-1 have all their gradients."""
+        if self._local_only:
+            self._launch_local_run(b0, b1)
+        else:
+            for b in range(b0, b1):
+                self._launch_bucket(self._buckets[b])
+
+    def _launch_local_run(self, b0: int, b1: int) -> None:
+        """world_size 1: ONE norm launch over a run of consecutive buckets (split where the gradient
+        dtype changes): per-tensor sums of squares of the gradients in place (ptr[1] = grad)."""
+        k = self._kernels
+        tab = self._unpack_table
+        bks = self._buckets[b0:b1]
+        i = 0
+        while i < len(bks):
+            gdt = None
+            j = i
+            ptrs = []
+            while j < len(bks):
+                gs = []
+                for p in bks[j].params:
+                    g = p.grad
+                    if g is None:
+                        raise RuntimeError("ddp_b200: gradient missing for a parameter marked ready")
+                    if not g.is_contiguous():
+                        g = g.contiguous()
+                        p.grad = g
+                    gs.append(g)
+                dts = {g.dtype for g in gs}
+                if len(dts) != 1:
+                    raise RuntimeError("ddp_b200: gradients of one bucket must share a dtype")
+                dt = dts.pop()
+                if gdt is None:
+                    gdt = dt
+                elif dt != gdt:
+                    break
+                ptrs.extend(g.data_ptr() for g in gs)
+                j += 1
+            first = bks[i].first
+            n = len(ptrs)
+            tab.host["ptr"][first:first + n, 1] = ptrs
+            k.sumsq(tab, gdt, self._sumsq[first:first + n], first=first, count=n, prefer_device=False)
+            self._stats["norm_launches"] += 1
+            i = j
 
     def _launch_bucket(self, bk: _Bucket) -> None:
         k = self._kernels
@@ -394,20 +448,8 @@ class DistributedDataParallel(nn.Module):
         hooked = self._comm_hook is not None
         # no hook: pre-divide, then SUM (div_factor_, reducer.hpp:497-500). With a hook the hook divides.
         scale = 1.0 if hooked else self._inv_world_size
-        local_only = self.world_size == 1 and not hooked
-        if local_only and not self.gradient_as_bucket_view:
-            # world_size 1, grads stay where autograd put them: nothing to exchange or copy, only the
-            # norm pass is left (ptr[1] = grad)
-            self._unpack_table.host["ptr"][first:first + n, 1] = self._pack_table.host["ptr"][first:first + n, 0]
-            k.sumsq(self._unpack_table, gdt, bk.sumsq, first=first, count=n, prefer_device=False)
-            self._stats["norm_launches"] += 1
-            return
-        # world_size 1 with bucket views: the norm rides on the pack pass
-        k.pack(self._pack_table, gdt, bk.dtype, scale, first=first, count=n,
-               sumsq_out=bk.sumsq if local_only else None, prefer_device=False)
+        k.pack(self._pack_table, gdt, bk.dtype, scale, first=first, count=n, prefer_device=False)
         self._stats["pack_launches"] += 1
-        if local_only:
-            return
         if hooked:
             gb = GradBucket(bk.index, bk.buffer, list(bk.views), list(bk.params), bk.index == len(self._buckets) - 1)
             bk.future = self._comm_hook(self._comm_hook_state, gb)
@@ -465,7 +507,7 @@ class DistributedDataParallel(nn.Module):
                 self._after_reduce(bk, [self._params[pi].grad for pi in bk.spec.indices])
         elif self._cuda and self.world_size > 1:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
-        if self.gradient_as_bucket_view:
+        if self.gradient_as_bucket_view and not self._local_only:
             for bk in self._buckets:
                 for pi, view in zip(bk.spec.indices, bk.views):
                     p = self._params[pi]
@@ -476,10 +518,14 @@ class DistributedDataParallel(nn.Module):
 
     # ---- beyond torch: feed gradients by hand, and the overlapped global norm ---------------------
     def reduce_gradients(self, grads: Optional[List[torch.Tensor]] = None,
-                         order: Optional[List[int]] = None) -> None:
+                         order: Optional[List[int]] = None,
+                         before_bucket: Optional[Callable[[int, List[int]], None]] = None) -> None:
         """Run one gradient synchronisation outside autograd: optionally install ``grads`` (one per
         parameter, registration order) as ``p.grad``, then mark parameters ready in ``order``
-        (default: the current bucket order) and finalize. Same scheduler as a real backward."""
+        (default: the current bucket order) and finalize. Same scheduler as a real backward.
+        ``before_bucket(bucket_index, parameter_indices)`` is called on the host right before each
+        bucket is launched (e.g. to make the stream wait for that bucket's gradients to arrive);
+        without it, buckets that need no exchange are coalesced into one launch."""
         self._rebuild_buckets()
         self._prepare_for_backward()
         if grads is not None:
@@ -489,7 +535,12 @@ class DistributedDataParallel(nn.Module):
             # every gradient is already there: walk the buckets in order, no per-parameter bookkeeping
             for bk in self._buckets:
                 bk.pending = 0
-                self._launch_bucket(bk)
+            if before_bucket is None:
+                self._launch_buckets(0, len(self._buckets))
+            else:
+                for b, bk in enumerate(self._buckets):
+                    before_bucket(b, bk.spec.indices)
+                    self._launch_buckets(b, b + 1)
             self._next_bucket = len(self._buckets)
         else:
             for pi in (order if order is not None else self._order):
@@ -516,7 +567,7 @@ class DistributedDataParallel(nn.Module):
         coef = out[1:2]
         if fused_optimizer is not None:
             fused_optimizer.set_clip_coef(coef)
-        elif self.gradient_as_bucket_view:
+        elif self.gradient_as_bucket_view and not self._local_only:
             for bk in self._buckets:
                 k.scale_by(self._view_table, bk.dtype, coef, first=bk.first, count=len(bk.spec.indices))
         else:
