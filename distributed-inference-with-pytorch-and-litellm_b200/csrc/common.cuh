@@ -15,6 +15,7 @@ namespace ddpb200 {
 constexpr int kThreads   = 256;   // threads per CTA
 constexpr int kTileElems = 2048;  // granularity of chunk sizes (elements)
 constexpr int kCtasPerSm = 3;     // persistent grid = SMs * kCtasPerSm (measured: 2-4 is the plateau, 8 loses 15 %)
+constexpr int kStreamCtasPerSm = 4;  // pack / norm: one or two streams, few registers: 4 CTAs/SM keep more loads in flight
 constexpr int kMaxValSegs = 448;  // segments that fit a by-value (launch-parameter) table
 
 // ---- segment tables ---------------------------------------------------------------

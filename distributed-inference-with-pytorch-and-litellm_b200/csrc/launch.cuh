@@ -21,10 +21,10 @@ inline int sm_count_cached(int* err) {
 
 // One CTA (or several, up to kCtasPerSm) per SM; CTAs walk the chunk list cyclically so that
 // neighbouring SMs stream neighbouring DRAM pages at the same time.
-inline int persistent_grid(int64_t total_chunks, int* err) {
+inline int persistent_grid(int64_t total_chunks, int* err, int ctas_per_sm = kCtasPerSm) {
   const int sms = sm_count_cached(err);
   if (sms <= 0) return 0;
-  const int64_t cap = (int64_t)sms * kCtasPerSm;
+  const int64_t cap = (int64_t)sms * ctas_per_sm;
   return (int)(total_chunks < cap ? total_chunks : cap);
 }
 

@@ -16,18 +16,19 @@ namespace ddpb200 {
 // left to the caller's scalar loop). NORM accumulates the squares of the values as stored.
 template <int SDT, int DDT, bool STORE, bool NORM, int VECB>
 __device__ __forceinline__ int64_t stream_chunk_vec(const char* src, char* dst, int64_t len, float scale,
-                                                    float& acc) {
+                                                    float (&acc)[4]) {
   constexpr bool any_f32 = (SDT == DDPB200_F32 || (STORE && DDT == DDPB200_F32));
   constexpr int G = GroupSize<VECB, any_f32>::G;
   const int64_t groups_end = len / G * G;
-#pragma unroll 2
+#pragma unroll 4
   for (int64_t i = (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
     float x[G];
     GroupIO<SDT, G>::load(src, i, x);
 #pragma unroll
     for (int k = 0; k < G; ++k) {
       float y = __fmul_rn(x[k], scale);
-      if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+      // four independent accumulators: a single one is a 4-cycle dependent chain per element
+      if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc[k & 3] = __fmaf_rn(y, y, acc[k & 3]); }
       x[k] = y;
     }
     if constexpr (STORE) GroupIO<DDT, G>::store(dst, i, x);
@@ -37,7 +38,7 @@ __device__ __forceinline__ int64_t stream_chunk_vec(const char* src, char* dst, 
 
 // SRC / DST: which ptr[] slot is read / written. STORE=false -> norm only.
 template <class Tab, int SDT, int DDT, int SRC, int DST, bool STORE, bool NORM, bool DEVSCALE>
-__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+__global__ void __launch_bounds__(kThreads, kStreamCtasPerSm)
 stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
               float scale, const float* __restrict__ scale_ptr, float* __restrict__ sumsq_out,
               float* __restrict__ chunk_partials, uint32_t* ticket) {
@@ -57,7 +58,7 @@ stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chu
     char* dst = nullptr;
     if constexpr (STORE) dst = static_cast<char*>(tab.ptr(s, DST)) + start * ElemOf<DDT>::size;
 
-    float acc = 0.f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
     bool a32 = group_aligned<SDT, G32>(src), a16 = group_aligned<SDT, G16>(src);
     if constexpr (STORE) { a32 = a32 && group_aligned<DDT, G32>(dst); a16 = a16 && group_aligned<DDT, G16>(dst); }
     int64_t done = 0;
@@ -66,12 +67,12 @@ stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chu
     // ragged end, or a segment whose base is not 16-byte aligned (odd element offset inside a bucket)
     for (int64_t i = done + threadIdx.x; i < len; i += kThreads) {
       float y = __fmul_rn(load1<SDT>(src, i), scale);
-      if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc = __fmaf_rn(y, y, acc); }
+      if constexpr (NORM) { y = round_through<STORE ? DDT : SDT>(y); acc[0] = __fmaf_rn(y, y, acc[0]); }
       if constexpr (STORE) store1<DDT>(dst, i, y);
     }
 
     if constexpr (NORM) {
-      const float total = block_sum(acc, red);
+      const float total = block_sum(__fadd_rn(__fadd_rn(acc[0], acc[1]), __fadd_rn(acc[2], acc[3])), red);
       if (threadIdx.x == 0) chunk_partials[c] = total;
     }
   }
@@ -91,7 +92,7 @@ static int launch_stream(const ddpb200_seg* table, int table_loc, int64_t n, int
     [&](auto& tab, int64_t chunks, int64_t seg_off, int64_t chunk_off) -> int {
       using Tab = std::remove_reference_t<decltype(tab)>;
       int err = 0;
-      int grid = persistent_grid(chunks, &err);
+      int grid = persistent_grid(chunks, &err, kStreamCtasPerSm);
       if (err) return err;
       if (grid == 0) {
         if (!NORM) return 0;

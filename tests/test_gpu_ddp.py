@@ -132,3 +132,16 @@ def _two_rank_worker(rank, ws, port):
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (gpurun --gpus 2)")
 def test_two_gpu_nccl_step_matches_stock_torch():
     mp.spawn(_two_rank_worker, args=(2, 29671), nprocs=2, join=True)
+
+
+def test_launch_script_single_gpu():
+    """scripts/run_node0.sh (the reference's launch line collapsed onto one box) trains a few steps
+    of the tiny model on the B200 path."""
+    import subprocess
+    env = dict(os.environ, NPROC="1", DDPB200_MODEL="tiny", DDPB200_MAX_STEPS="5", DDPB200_SEQ_LEN="64",
+               MASTER_PORT="29741")
+    env.pop("MASTER_ADDR", None)
+    res = subprocess.run(["bash", os.path.join(ROOT, "scripts", "run_node0.sh")], cwd=ROOT, env=env,
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-3000:]
+    assert "done: 5 steps" in res.stderr and "Using device: cuda:0" in res.stderr
