@@ -367,30 +367,37 @@ def run_ours(args):
 
 
 def measure_allreduce(ddp, ws, dev):
-    """busbw = S/t * 2(n-1)/n over the model's own buckets, back to back on one stream."""
+    """Bus bandwidth of the path's gradient collective, measured alone: busbw = S/t * 2(n-1)/n
+    (NCCL-tests convention). `coalesced` is what a step of this bench issues (all buckets complete at
+    once -> one allreduce over the contiguous bucket arena); `per_bucket` is what a real backward
+    issues (one allreduce per 25 MiB-capped bucket, back to back on one stream)."""
+    def timed(fn, reps=5):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / reps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
     bufs = [bk.buffer for bk in ddp._buckets]
+    arenas = list(ddp._arenas.values())
     S = sum(b.numel() * b.element_size() for b in bufs)
-    for _ in range(2):
-        for b in bufs:
-            dist.all_reduce(b)
-    torch.cuda.synchronize()
-    dist.barrier()
-    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    reps = 5
-    for _ in range(reps):
-        for b in bufs:
-            dist.all_reduce(b)
-    b_.record()
-    torch.cuda.synchronize()
-    t = torch.tensor([a.elapsed_time(b_) / reps], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t)
-    for b in bufs:
-        b.zero_()
-    bus = S / (ms * 1e-3) * 2 * (ws - 1) / ws / 1e9
-    return {"bytes_per_step": S, "ms_per_step": ms, "busbw_gbs": bus, "frac_of_900": bus / 900.0,
-            "buckets": len(bufs)}
+    Sa = sum(a.numel() * a.element_size() for a in arenas)
+    ms_one = timed(lambda: [dist.all_reduce(a) for a in arenas])
+    ms_per = timed(lambda: [dist.all_reduce(b) for b in bufs])
+    for a in arenas:
+        a.zero_()
+    f = 2 * (ws - 1) / ws / 1e9
+    return {"bytes_per_step": S, "buckets": len(bufs),
+            "coalesced": {"ms": ms_one, "busbw_gbs": Sa / (ms_one * 1e-3) * f, "frac_of_900": Sa / (ms_one * 1e-3) * f / 900.0},
+            "per_bucket": {"ms": ms_per, "busbw_gbs": S / (ms_per * 1e-3) * f, "frac_of_900": S / (ms_per * 1e-3) * f / 900.0}}
 
 
 # ---- CPU baselines --------------------------------------------------------------------------------

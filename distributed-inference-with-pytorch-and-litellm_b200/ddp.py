@@ -67,7 +67,7 @@ class GradBucket:
 
 class _Bucket:
     __slots__ = ("index", "spec", "buffer", "views", "first", "n", "params", "sumsq", "pending", "future",
-                 "work", "dtype")
+                 "work", "dtype", "arena_start")
 
     def __init__(self, index, spec, buffer, views, first, params):
         self.index, self.spec, self.buffer, self.views, self.first = index, spec, buffer, views, first
@@ -148,6 +148,7 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._next_bucket = 0
         self._sumsq_valid = False
+        self._coalesce = False
         self._stats = {"iterations": 0, "pack_launches": 0, "allreduces": 0, "norm_launches": 0,
                        "unpack_launches": 0, "rebuilt_bucket_sizes": []}
 
@@ -228,12 +229,26 @@ class DistributedDataParallel(nn.Module):
         specs = bucketing.layout_buckets(numels, bucket_indices, limits)
         self._buckets: List[_Bucket] = []
         self._order: List[int] = []
+        # All buckets of one dtype are carved out of ONE arena, in bucket order, each starting on a
+        # 128-element boundary: inside a bucket the layout is torch's (no padding), and a run of
+        # consecutive buckets is one contiguous range, so it can be packed, allreduced and normed as a
+        # single launch / a single collective when all of its gradients are present at once.
+        align = 128
+        arena_len, starts = {}, []
+        for spec in specs:
+            dt = self._params[spec.indices[0]].dtype
+            off = (arena_len.get(dt, 0) + align - 1) // align * align
+            starts.append(off)
+            arena_len[dt] = off + spec.numel
+        self._arenas = {dt: torch.zeros(max(n, 1), dtype=dt, device=self.device) for dt, n in arena_len.items()}
         first = 0
         for b, spec in enumerate(specs):
             dt = self._params[spec.indices[0]].dtype
-            buf = torch.zeros(spec.numel, dtype=dt, device=self.device)
+            buf = self._arenas[dt][starts[b]:starts[b] + spec.numel]
             views = [buf[o:o + numels[i]].view_as(self._params[i]) for i, o in zip(spec.indices, spec.offsets)]
-            self._buckets.append(_Bucket(b, spec, buf, views, first, [self._params[i] for i in spec.indices]))
+            bk = _Bucket(b, spec, buf, views, first, [self._params[i] for i in spec.indices])
+            bk.arena_start = starts[b]
+            self._buckets.append(bk)
             self._order.extend(spec.indices)
             first += len(spec.indices)
         n = len(self._order)
@@ -386,9 +401,65 @@ class DistributedDataParallel(nn.Module):
         """Buckets b0..b1-1 have all their gradients."""
         if self._local_only:
             self._launch_local_run(b0, b1)
+        elif self._coalesce and self._comm_hook is None and b1 - b0 > 1:
+            self._launch_coalesced(b0, b1)
         else:
             for b in range(b0, b1):
                 self._launch_bucket(self._buckets[b])
+
+    def _launch_coalesced(self, b0: int, b1: int) -> None:
+        """Buckets b0..b1-1 are complete AT ONCE and every rank knows it (manual gradient feed): per
+        run of equal dtype ONE pack launch, ONE allreduce over the contiguous arena range, ONE norm
+        (or unpack+norm) launch. Not used from autograd hooks, where ranks could disagree on which
+        buckets happen to be complete together."""
+        k = self._kernels
+        i = b0
+        while i < b1:
+            j = i
+            dt = self._buckets[i].dtype
+            grads = []
+            while j < b1 and self._buckets[j].dtype == dt:
+                for p in self._buckets[j].params:
+                    g = p.grad
+                    if g is None:
+                        raise RuntimeError("ddp_b200: gradient missing for a parameter marked ready")
+                    if not g.is_contiguous():
+                        g = g.contiguous()
+                        p.grad = g
+                    grads.append(g)
+                j += 1
+            gdt = grads[0].dtype
+            if any(g.dtype != gdt for g in grads):
+                raise RuntimeError("ddp_b200: gradients of one dtype group must share a dtype")
+            first, n = self._buckets[i].first, len(grads)
+            last = self._buckets[j - 1]
+            span = self._arenas[dt][self._buckets[i].arena_start:last.arena_start + last.spec.numel]
+            self._pack_table.host["ptr"][first:first + n, 0] = [g.data_ptr() for g in grads]
+            k.pack(self._pack_table, gdt, dt, self._inv_world_size, first=first, count=n, prefer_device=False)
+            self._stats["pack_launches"] += 1
+
+            def behind():
+                if self.gradient_as_bucket_view:
+                    k.sumsq(self._view_table, dt, self._sumsq[first:first + n], first=first, count=n)
+                    self._stats["norm_launches"] += 1
+                else:
+                    self._unpack_table.host["ptr"][first:first + n, 1] = [g.data_ptr() for g in grads]
+                    k.pack(self._unpack_table, dt, gdt, 1.0, first=first, count=n,
+                           sumsq_out=self._sumsq[first:first + n], prefer_device=False)
+                    self._stats["unpack_launches"] += 1
+
+            if self._cuda:
+                ev = torch.cuda.Event()
+                ev.record()
+                with torch.cuda.stream(self._comm_stream):
+                    self._comm_stream.wait_event(ev)
+                    dist.all_reduce(span, group=self.process_group, async_op=True).wait()
+                    behind()
+            else:
+                dist.all_reduce(span, group=self.process_group)
+                behind()
+            self._stats["allreduces"] += 1
+            i = j
 
     def _launch_local_run(self, b0: int, b1: int) -> None:
         """world_size 1: ONE norm launch over a run of consecutive buckets (split where the gradient
@@ -536,7 +607,11 @@ class DistributedDataParallel(nn.Module):
             for bk in self._buckets:
                 bk.pending = 0
             if before_bucket is None:
-                self._launch_buckets(0, len(self._buckets))
+                self._coalesce = True           # every rank takes this branch with every bucket complete
+                try:
+                    self._launch_buckets(0, len(self._buckets))
+                finally:
+                    self._coalesce = False
             else:
                 for b, bk in enumerate(self._buckets):
                     before_bucket(b, bk.spec.indices)

@@ -179,3 +179,39 @@ def test_adamw_state_dict_and_table_reuse(native_lib):
         assert torch.allclose(p, q, rtol=3e-6, atol=1e-7)
     with pytest.raises(NotImplementedError):
         ddp_b200.AdamW(ps, amsgrad=True)
+
+
+def _worker_coalesced_feed(rank, ws, port):
+    """reduce_gradients with every gradient present: one pack / one allreduce / one norm launch for
+    all buckets, same averaged gradients and norm as the bucket-by-bucket path."""
+    _setup(rank, ws, port)
+    import copy
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    mg = _load_golden_module()
+    torch.manual_seed(0)
+    base = mg.SmallNet()
+    nets = [copy.deepcopy(base) for _ in range(3)]
+    ka, kb, kc = OracleKernels(), OracleKernels(), OracleKernels()
+    one = ddp_b200.DistributedDataParallel(nets[0], bucket_cap_mb=0.008, gradient_as_bucket_view=True, kernels=ka)
+    per = ddp_b200.DistributedDataParallel(nets[1], bucket_cap_mb=0.008, gradient_as_bucket_view=True, kernels=kb)
+    cop = ddp_b200.DistributedDataParallel(nets[2], bucket_cap_mb=0.008, gradient_as_bucket_view=False, kernels=kc)
+    order = [7, 6, 5, 3, 4, 2, 1, 0]
+    for s in range(3):
+        g = torch.Generator().manual_seed(50 + 10 * s + rank)
+        grads = [torch.randn(p.shape, generator=g) for p in base.parameters()]
+        for d, kw in ((one, {}), (per, dict(before_bucket=lambda b, idx: None)), (cop, {})):
+            d.reduce_gradients([x.clone() for x in grads], order=order if s == 0 else None, **kw)
+        for pa, pb, pc in zip(nets[0].parameters(), nets[1].parameters(), nets[2].parameters()):
+            assert torch.equal(pa.grad, pb.grad) and torch.equal(pa.grad, pc.grad)
+        na, nb, nc = one.clip_grad_norm_(1e9), per.clip_grad_norm_(1e9), cop.clip_grad_norm_(1e9)
+        assert float(na) == float(nb) == float(nc)
+    assert len(one.bucket_layout()) == 3
+    # steps 1 and 2 ran on the 3 rebuilt buckets: coalesced = 1 pack each, bucket-by-bucket = 3 each
+    assert ka.calls["pack"] == 1 + 2 * 1 and kb.calls["pack"] == 1 + 2 * 3
+    assert one._get_ddp_logging_data()["allreduces"] == 3 and per._get_ddp_logging_data()["allreduces"] == 1 + 2 * 3
+    dist.destroy_process_group()
+
+
+def test_coalesced_gradient_feed(native_lib):
+    mp.spawn(_worker_coalesced_feed, args=(2, 29661), nprocs=2, join=True)
