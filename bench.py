@@ -202,7 +202,8 @@ def run_ours(args):
     numel = [p.numel() for p in params]
     total = sum(numel)
     esize = 2
-    ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
+    ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
+                                           fused_allreduce=(args.allreduce == "fused"))
     opt = ddp_b200.AdamW(params, lr=LR, weight_decay=1e-2)
 
     # synthetic gradients, resident in HBM, one tensor per parameter (rank-dependent values)
@@ -254,6 +255,7 @@ def run_ours(args):
     stats1 = dict(ddp._get_ddp_logging_data())
     launches = sum(stats1[k] - stats0[k] for k in ("pack_launches", "norm_launches", "unpack_launches"))
     launches += args.steps * (1 + opt.launches_last_step)          # finalize + fused AdamW per step
+    launches += 2 * (stats1.get("fused_allreduces", 0) - stats0.get("fused_allreduces", 0))   # allreduce kernel + fold
     allreduces = stats1["allreduces"] - stats0["allreduces"]
 
     # ---- timed: end to end from HOST gradients ---------------------------------------------------
@@ -344,7 +346,9 @@ def run_ours(args):
                     "note": "gradients of each step copied from pinned host memory (bucket by bucket, double "
                             "buffered); total norm read back on the host every step"},
             "gpu_launches": launches,
-            "nccl_allreduces": allreduces,
+            "nccl_allreduces": 0 if ddp._fused else allreduces,
+            "fused_allreduces": stats1.get("fused_allreduces", 0) - stats0.get("fused_allreduces", 0),
+            "allreduce_impl": "fused peer-memory kernel" if ddp._fused else ("nccl" if ws > 1 else "none"),
             "roofline": {"kernel": "adamw_kernel (fused clip+AdamW, bf16)", "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                          "frac_of_8000_nominal": achieved / 8000.0, "algorithmic_bytes_per_launch": alg_bytes,
@@ -488,6 +492,8 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=list(WORKLOADS), default="llama-3.2-1b")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--allreduce", choices=["nccl", "fused"], default=os.environ.get("DDPB200_BENCH_ALLREDUCE", "nccl"),
+                    help="N>1: NCCL allreduce + norm launch, or the fused peer-memory allreduce+norm kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

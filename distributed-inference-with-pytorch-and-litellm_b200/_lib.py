@@ -28,6 +28,14 @@ class Seg(ctypes.Structure):
 
 
 assert ctypes.sizeof(Seg) == 48
+MAX_PEERS = 8
+
+
+class PeerMap(ctypes.Structure):
+    """struct ddpb200_peer_map"""
+    _fields_ = [("arena", ctypes.c_void_p * MAX_PEERS), ("partials", ctypes.c_void_p * MAX_PEERS),
+                ("arena_multicast", ctypes.c_void_p), ("rank", ctypes.c_int32), ("world", ctypes.c_int32)]
+
 
 _vp, _i64, _i32, _u32, _f32, _f64 = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_uint32,
                                      ctypes.c_float, ctypes.c_double)
@@ -49,6 +57,8 @@ SIGNATURES = {
     "ddpb200_fused_clip_adamw": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _f64, _vp,
                                                 _f64, _f64, _f64, _f64, _i64, _vp, _vp, _vp, _u32, _vp]),
     "ddpb200_adamw_bias_corrections": (ctypes.c_int, [_f64, _f64, _i64, _vp]),
+    "ddpb200_allreduce_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _vp]),
+    "ddpb200_fold_chunk_partials": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
 }
 
 

@@ -1,0 +1,224 @@
+// Bucket allreduce fused with the gradient-norm pass, over NVLink peer memory / NVSwitch multicast.
+//
+// Replaces, for the bucket arena of one dtype, the pair  ncclAllReduce(SUM)  (c10d Reducer,
+// TORCH/include/torch/csrc/distributed/c10d/reducer.hpp:524)  +  torch._foreach_norm
+// (TORCH/nn/utils/clip_grad.py:96)  by ONE kernel per rank that moves every gradient byte once:
+//
+//   chunk c belongs to rank c % world. The owner reads the chunk from EVERY rank's arena
+//     - peer mode:      one 256-bit load per rank over NVLink, summed in fp32 in rank order 0..n-1
+//     - multicast mode: multimem.ld_reduce (the NVSwitch adds the n copies, fp32 accumulation)
+//   rounds once to the bucket dtype, accumulates the squares of what it stores, and writes the
+//   result into every rank's arena (n peer stores, or one multimem.st that the switch replicates).
+//   The chunk's sum of squares goes to every rank's partials array, so that after a barrier each
+//   rank folds the same numbers in the same order (ddpb200_fold_chunk_partials): norms are
+//   bitwise identical on all ranks, and so is every averaged gradient (one owner computes it).
+//
+// NVLink bytes per GPU and direction for S bytes of gradients: peer mode 2(n-1)/n * S (as a ring),
+// multicast mode (1 + 1/n) * S. Multicast wins from 4 ranks up; at 2 ranks peer mode moves less.
+// The arena must be symmetric memory (same offset on every rank); the caller provides the barriers
+// (all ranks packed before this kernel; all ranks finished it before anyone reads the arena).
+#include "launch.cuh"
+
+namespace ddpb200 {
+
+struct PeerMap {                        // device-side copy of ddpb200_peer_map
+  char* arena[DDPB200_MAX_PEERS];
+  float* partials[DDPB200_MAX_PEERS];
+  char* mc;
+  int rank, world;
+};
+
+__device__ __forceinline__ Raw<4> mc_ld_reduce_bf16x8(const void* p) {
+  Raw<4> x;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]) : "l"(__cvta_generic_to_global(p)) : "memory");
+  return x;
+}
+__device__ __forceinline__ Raw<4> mc_ld_reduce_f32x4(const void* p) {
+  Raw<4> x;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]) : "l"(__cvta_generic_to_global(p)) : "memory");
+  return x;
+}
+__device__ __forceinline__ void mc_st_128(void* p, const Raw<4>& x) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(__cvta_generic_to_global(p)), "r"(x.r[0]), "r"(x.r[1]), "r"(x.r[2]), "r"(x.r[3]) : "memory");
+}
+
+template <int DT> __device__ __forceinline__ void unpack128(const Raw<4>& t, float (&v)[16 / ElemOf<DT>::size]) {
+  if constexpr (DT == DDPB200_F32) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = __uint_as_float(t.r[k]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { v[2 * k] = bf16_bits_to_f32(t.r[k] & 0xffffu); v[2 * k + 1] = __uint_as_float(t.r[k] & 0xffff0000u); }
+  }
+}
+
+// MC: 1 = multicast (multimem) for the vector body, 0 = peer loads/stores.
+template <int DT, int MC>
+__global__ void __launch_bounds__(kThreads, 2)
+fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, const __grid_constant__ PeerMap pm) {
+  constexpr int ES = ElemOf<DT>::size;
+  constexpr int G = 32 / ES;            // 256-bit groups in peer mode
+  constexpr int H = 16 / ES;            // 128-bit groups in multicast mode
+  __shared__ float red[kThreads / 32];
+  const int64_t chunk_base = tab.begin(0);
+  const int world = pm.world;
+  char* const local = pm.arena[pm.rank];
+
+  for (int64_t c = pm.rank + (int64_t)world * blockIdx.x; c < total_chunks; c += (int64_t)world * gridDim.x) {
+    const int s = find_seg(tab, c + chunk_base);
+    const int64_t start = (c + chunk_base - tab.begin(s)) * chunk_elems;
+    const int64_t rest = tab.numel(s) - start;
+    const int64_t len = rest < chunk_elems ? rest : chunk_elems;
+    const int64_t off = (static_cast<char*>(tab.ptr(s, 1)) - local) + start * ES;     // byte offset in the arena
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    int64_t done = 0;
+
+    if (MC && (off % 16) == 0) {
+      const int64_t groups_end = len / H * H;
+#pragma unroll 4
+      for (int64_t i = (int64_t)threadIdx.x * H; i < groups_end; i += kThreads * H) {
+        Raw<4> t;
+        if constexpr (DT == DDPB200_F32) t = mc_ld_reduce_f32x4(pm.mc + off + i * ES);
+        else t = mc_ld_reduce_bf16x8(pm.mc + off + i * ES);
+        float v[H];
+        unpack128<DT>(t, v);
+#pragma unroll
+        for (int k = 0; k < H; ++k) acc[k & 3] = __fmaf_rn(v[k], v[k], acc[k & 3]);
+        mc_st_128(pm.mc + off + i * ES, t);
+      }
+      done = groups_end;
+    } else if (!MC && (off % 32) == 0) {
+      const int64_t groups_end = len / G * G;
+#pragma unroll 1
+      for (int64_t i = (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
+        Raw<8> raw[DDPB200_MAX_PEERS];
+#pragma unroll
+        for (int p = 0; p < DDPB200_MAX_PEERS; ++p)                       // all loads in flight first
+          if (p < world) raw[p] = ldg256(pm.arena[p] + off + i * ES);
+        float sum[G];
+#pragma unroll
+        for (int k = 0; k < G; ++k) sum[k] = 0.f;
+#pragma unroll
+        for (int p = 0; p < DDPB200_MAX_PEERS; ++p)
+          if (p < world) {                                                 // rank order: same bits everywhere
+            if constexpr (DT == DDPB200_F32) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) sum[k] = __fadd_rn(sum[k], __uint_as_float(raw[p].r[k]));
+            } else {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                sum[2 * k] = __fadd_rn(sum[2 * k], bf16_bits_to_f32(raw[p].r[k] & 0xffffu));
+                sum[2 * k + 1] = __fadd_rn(sum[2 * k + 1], __uint_as_float(raw[p].r[k] & 0xffff0000u));
+              }
+            }
+          }
+        Raw<8> out;
+        if constexpr (DT == DDPB200_F32) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { acc[k & 3] = __fmaf_rn(sum[k], sum[k], acc[k & 3]); out.r[k] = __float_as_uint(sum[k]); }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            out.r[k] = pack_bf16x2(sum[2 * k], sum[2 * k + 1]);
+            const float lo = bf16_bits_to_f32(out.r[k] & 0xffffu), hi = __uint_as_float(out.r[k] & 0xffff0000u);
+            acc[(2 * k) & 3] = __fmaf_rn(lo, lo, acc[(2 * k) & 3]);
+            acc[(2 * k + 1) & 3] = __fmaf_rn(hi, hi, acc[(2 * k + 1) & 3]);
+          }
+        }
+#pragma unroll
+        for (int p = 0; p < DDPB200_MAX_PEERS; ++p)
+          if (p < world) stg256(pm.arena[p] + off + i * ES, out);
+      }
+      done = groups_end;
+    }
+    // ragged end / misaligned segment: element by element through the peer mappings
+    for (int64_t i = done + threadIdx.x; i < len; i += kThreads) {
+      float sum = 0.f;
+      for (int p = 0; p < world; ++p) sum = __fadd_rn(sum, load1<DT>(pm.arena[p] + off, i));
+      sum = round_through<DT>(sum);
+      acc[0] = __fmaf_rn(sum, sum, acc[0]);
+      for (int p = 0; p < world; ++p) store1<DT>(pm.arena[p] + off, i, sum);
+    }
+
+    const float total = block_sum(__fadd_rn(__fadd_rn(acc[0], acc[1]), __fadd_rn(acc[2], acc[3])), red);
+    if (threadIdx.x == 0)
+      for (int p = 0; p < world; ++p) pm.partials[p][c] = total;
+  }
+  __threadfence_system();               // peer stores are out before the kernel is reported complete
+}
+
+// Per-segment fold of the chunk partials, fixed order (the tail of finish_sumsq as its own launch:
+// here the partials come from other GPUs, so a cross-GPU barrier sits between the two kernels).
+__global__ void __launch_bounds__(kThreads, 1)
+fold_partials_kernel(DevTable tab, int64_t total_chunks, const float* __restrict__ partials,
+                     float* __restrict__ sumsq_out) {
+  const int64_t chunk_base = tab.begin(0);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (kThreads / 32) * gridDim.x;
+  for (int s = blockIdx.x * (kThreads / 32) + warp; s < tab.n; s += nwarps) {
+    const int64_t b = tab.begin(s) - chunk_base;
+    const int64_t e = (s + 1 < tab.n) ? tab.begin(s + 1) - chunk_base : total_chunks;
+    double acc = 0.0;
+    for (int64_t c = b + lane; c < e; c += 32) acc += (double)__ldcg(partials + c);
+    acc = warp_sum(acc);
+    if (lane == 0) sumsq_out[s] = (float)acc;
+  }
+}
+
+}  // namespace ddpb200
+
+using namespace ddpb200;
+
+extern "C" DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n,
+                                                          int64_t total_chunks, int64_t chunk_elems,
+                                                          int32_t dtype, const ddpb200_peer_map* peers,
+                                                          int32_t use_multicast, void* stream) {
+  if (!valid_chunking(n, total_chunks, chunk_elems) || !dev_table || !peers) return DDPB200_E_INVALID;
+  if (peers->world < 1 || peers->world > DDPB200_MAX_PEERS || peers->rank < 0 || peers->rank >= peers->world)
+    return DDPB200_E_INVALID;
+  if (use_multicast && !peers->arena_multicast) return DDPB200_E_INVALID;
+  if (n == 0 || total_chunks == 0) return 0;
+  PeerMap pm;
+  for (int p = 0; p < DDPB200_MAX_PEERS; ++p) {
+    pm.arena[p] = p < peers->world ? static_cast<char*>(peers->arena[p]) : nullptr;
+    pm.partials[p] = p < peers->world ? peers->partials[p] : nullptr;
+    if (p < peers->world && (!pm.arena[p] || !pm.partials[p])) return DDPB200_E_INVALID;
+  }
+  pm.mc = static_cast<char*>(peers->arena_multicast);
+  pm.rank = peers->rank;
+  pm.world = peers->world;
+  int err = 0;
+  const int sms = sm_count_cached(&err);
+  if (err) return err;
+  const int64_t mine = (total_chunks - pm.rank + pm.world - 1) / pm.world;     // chunks this rank owns
+  const int64_t cap = (int64_t)sms * 2;
+  const int grid = (int)(mine < cap ? (mine > 0 ? mine : 1) : cap);
+  DevTable tab{dev_table, (int)n};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define DDPB200_AR_CASE(DT)                                                                          \
+  if (dtype == DT) {                                                                                 \
+    if (use_multicast) fused_allreduce_kernel<DT, 1><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm); \
+    else fused_allreduce_kernel<DT, 0><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm);                \
+    return (int)cudaGetLastError();                                                                  \
+  }
+  DDPB200_AR_CASE(DDPB200_BF16)
+  DDPB200_AR_CASE(DDPB200_F32)
+#undef DDPB200_AR_CASE
+  return DDPB200_E_UNSUPPORTED;
+}
+
+extern "C" DDPB200_API int ddpb200_fold_chunk_partials(const ddpb200_seg* dev_table, int64_t n,
+                                                       int64_t total_chunks, const float* chunk_partials,
+                                                       float* sumsq_out, void* stream) {
+  if (n < 0 || n > INT32_MAX || total_chunks < 0 || (n > 0 && (!dev_table || !sumsq_out)) ||
+      (total_chunks > 0 && !chunk_partials))
+    return DDPB200_E_INVALID;
+  if (n == 0) return 0;
+  DevTable tab{dev_table, (int)n};
+  const int grid = (int)((n + 7) / 8 < 64 ? (n + 7) / 8 : 64);
+  fold_partials_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(tab, total_chunks, chunk_partials, sumsq_out);
+  return (int)cudaGetLastError();
+}

@@ -23,6 +23,7 @@ modules and ``join()`` are outside the path this package covers and raise.
 """
 from __future__ import annotations
 
+import os
 import sys
 import weakref
 from contextlib import contextmanager
@@ -87,7 +88,8 @@ class DistributedDataParallel(nn.Module):
                  check_reduction: bool = False, gradient_as_bucket_view: bool = False,
                  static_graph: bool = False, delay_all_reduce_named_params=None,
                  param_to_hook_all_reduce=None, mixed_precision=None, device_mesh=None,
-                 skip_all_reduce_unused_params: bool = False, *, kernels=None):
+                 skip_all_reduce_unused_params: bool = False, *, kernels=None,
+                 fused_allreduce: Optional[bool] = None):
         super().__init__()
         if find_unused_parameters:
             raise NotImplementedError("ddp_b200: find_unused_parameters=True is outside the hot path covered")
@@ -139,6 +141,11 @@ class DistributedDataParallel(nn.Module):
             self._sync_module_states()
 
         self._comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self._cuda else None
+        # bucket allreduce + norm as ONE kernel over NVLink peer memory instead of NCCL + a norm pass
+        if fused_allreduce is None:
+            fused_allreduce = os.environ.get("DDPB200_FUSED_ALLREDUCE", "0") == "1"
+        self._fused = bool(fused_allreduce) and self._cuda and 1 < self.world_size <= 8
+        self._sym = {}
         self._comm_hook: Optional[Callable] = None
         self._comm_hook_state = None
         self._hook_handles = []
@@ -240,7 +247,14 @@ class DistributedDataParallel(nn.Module):
             off = (arena_len.get(dt, 0) + align - 1) // align * align
             starts.append(off)
             arena_len[dt] = off + spec.numel
-        self._arenas = {dt: torch.zeros(max(n, 1), dtype=dt, device=self.device) for dt, n in arena_len.items()}
+        if self._fused:
+            from .symm import SymmetricArena
+            max_chunks = sum(p.numel() for p in self._params) // 2048 + len(self._params) + 1
+            self._sym = {dt: SymmetricArena(n, dt, self.device, self.process_group, max_chunks)
+                         for dt, n in sorted(arena_len.items(), key=lambda kv: str(kv[0]))}
+            self._arenas = {dt: a.tensor for dt, a in self._sym.items()}
+        else:
+            self._arenas = {dt: torch.zeros(max(n, 1), dtype=dt, device=self.device) for dt, n in arena_len.items()}
         first = 0
         for b, spec in enumerate(specs):
             dt = self._params[spec.indices[0]].dtype
@@ -448,7 +462,13 @@ class DistributedDataParallel(nn.Module):
                            sumsq_out=self._sumsq[first:first + n], prefer_device=False)
                     self._stats["unpack_launches"] += 1
 
-            if self._cuda:
+            if self._fused:
+                ev = torch.cuda.Event()
+                ev.record()
+                with torch.cuda.stream(self._comm_stream):
+                    self._comm_stream.wait_event(ev)
+                    self._fused_reduce(dt, gdt, first, n, grads)
+            elif self._cuda:
                 ev = torch.cuda.Event()
                 ev.record()
                 with torch.cuda.stream(self._comm_stream):
@@ -526,7 +546,13 @@ class DistributedDataParallel(nn.Module):
             bk.future = self._comm_hook(self._comm_hook_state, gb)
             self._stats["allreduces"] += 1
             return
-        if self._cuda:
+        if self._fused:
+            ev = torch.cuda.Event()
+            ev.record()
+            with torch.cuda.stream(self._comm_stream):
+                self._comm_stream.wait_event(ev)
+                self._fused_reduce(bk.dtype, gdt, first, n, grads)
+        elif self._cuda:
             ev = torch.cuda.Event()
             ev.record()
             with torch.cuda.stream(self._comm_stream):
@@ -538,6 +564,18 @@ class DistributedDataParallel(nn.Module):
             dist.all_reduce(bk.buffer, group=self.process_group)
             self._after_reduce(bk, grads)
         self._stats["allreduces"] += 1
+
+    def _fused_reduce(self, dt, gdt, first: int, n: int, grads: List[torch.Tensor]) -> None:
+        """Rows [first, first+n) of the arena: SUM over ranks in place + per-tensor sums of squares in
+        one kernel over NVLink peer memory (csrc/fused_allreduce.cu), then the copy back into p.grad
+        unless gradients are bucket views."""
+        k = self._kernels
+        k.allreduce_sumsq(self._view_table, dt, self._sym[dt], self._sumsq[first:first + n], first=first, count=n)
+        self._stats["fused_allreduces"] = self._stats.get("fused_allreduces", 0) + 1
+        if not self.gradient_as_bucket_view:
+            self._unpack_table.host["ptr"][first:first + n, 1] = [g.data_ptr() for g in grads]
+            k.pack(self._unpack_table, dt, gdt, 1.0, first=first, count=n, prefer_device=False)
+            self._stats["unpack_launches"] += 1
 
     def _after_reduce(self, bk: _Bucket, grads: List[torch.Tensor]) -> None:
         """Behind the allreduce, on the same stream: per-tensor sum of squares of the averaged

@@ -230,6 +230,28 @@ class CudaKernels:
         _lib.check(rc, "ddpb200_fused_clip_adamw")
 
 
+    # ---- fused bucket allreduce + norm over peer memory ---------------------------------------
+    def allreduce_sumsq(self, tab: SegTable, dtype: torch.dtype, arena, sumsq_out: torch.Tensor,
+                        first: int = 0, count: Optional[int] = None) -> None:
+        """SUM over ranks of rows [first, first+count) of the symmetric bucket arena, in place on
+        every rank, and their per-tensor sums of squares into sumsq_out — barrier, one kernel,
+        barrier, fold; all on the current stream."""
+        if tab.dev is None:
+            raise RuntimeError("allreduce_sumsq needs the device-resident table of bucket views")
+        ptr, _, n, chunks = tab.args(first, count, True)
+        chunk_off = int(tab.chunk_begins[first])
+        st = self._stream()
+        L = _lib.lib()
+        arena.barrier()                                   # every rank has packed this range
+        pm = arena.peer_map(chunk_off)
+        _lib.check(L.ddpb200_allreduce_sumsq_chunks(ptr, n, chunks, tab.chunk_elems, dtype_code(dtype),
+                                                    ctypes.addressof(pm), int(arena.use_multicast), st),
+                   "ddpb200_allreduce_sumsq_chunks")
+        arena.barrier()                                   # every rank has written its chunks everywhere
+        _lib.check(L.ddpb200_fold_chunk_partials(ptr, n, chunks, arena.partials.data_ptr() + 4 * chunk_off,
+                                                 sumsq_out.data_ptr(), st), "ddpb200_fold_chunk_partials")
+
+
 _default: Optional[CudaKernels] = None
 
 

@@ -170,6 +170,35 @@ DDPB200_API int ddpb200_scale_by_device_scalar(const ddpb200_seg* table, int32_t
                                    int64_t total_chunks, int64_t chunk_elems, int32_t dtype,
                                    const float* coef, void* stream);
 
+/* ---- a-3 + a-5  bucket allreduce fused with the norm pass, over NVLink peer memory -------------
+ * Replaces ProcessGroupNCCL::allreduce on the buckets (c10d Reducer all_reduce_bucket,
+ * TORCH/include/torch/csrc/distributed/c10d/reducer.hpp:524) followed by torch._foreach_norm
+ * (TORCH/nn/utils/clip_grad.py:96): SUM over ranks of the (pre-scaled) bucket arena, in place on every
+ * rank, and the per-chunk sums of squares of the result, in one pass.
+ * The arena must be symmetric memory: every rank's copy mapped into this process (arena[p]), same
+ * layout on all ranks; arena_multicast is its NVSwitch multicast address or NULL. dev_table is this
+ * rank's DEVICE table with ptr[1] = bucket views inside arena[rank]. Chunk c is reduced by rank
+ * c % world and written to all ranks; its sum of squares is written to partials[p][c] on all ranks.
+ * use_multicast != 0: multimem.ld_reduce / multimem.st through the switch ((1+1/n)*S NVLink bytes per
+ * GPU and direction); 0: 256-bit peer loads and stores (2(n-1)/n*S), fp32 sum in rank order.
+ * The CALLER orders the ranks: a barrier after every rank has packed and before this call, and a
+ * barrier after it before anyone reads the arena or the partials (then ddpb200_fold_chunk_partials
+ * gives sumsq_out[n], bitwise identical on every rank). */
+#define DDPB200_MAX_PEERS 8
+typedef struct ddpb200_peer_map {
+  void*   arena[DDPB200_MAX_PEERS];
+  float*  partials[DDPB200_MAX_PEERS];
+  void*   arena_multicast;
+  int32_t rank;
+  int32_t world;
+} ddpb200_peer_map;
+DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
+                                               int64_t chunk_elems, int32_t dtype,
+                                               const ddpb200_peer_map* peers, int32_t use_multicast,
+                                               void* stream);
+DDPB200_API int ddpb200_fold_chunk_partials(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
+                                            const float* chunk_partials, float* sumsq_out, void* stream);
+
 /* ---- a-6  fused unscale + clip + AdamW ---------------------------------------
  * Replaces torch.optim.AdamW.step (TORCH/optim/adamw.py:20-49, TORCH/optim/adam.py:
  * 215-272; element math of TORCH/include/ATen/native/cuda/fused_adam_utils.cuh:41-93,

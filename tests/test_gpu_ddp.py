@@ -25,7 +25,7 @@ def _golden_module():
     return mod
 
 
-def _train_compare(rank, ws, dtype, gabv, steps=5, fold_clip=True):
+def _train_compare(rank, ws, dtype, gabv, steps=5, fold_clip=True, fused=False):
     import ddp_b200
     mg = _golden_module()
     dev = torch.device("cuda", rank if ws > 1 else 0)
@@ -35,7 +35,7 @@ def _train_compare(rank, ws, dtype, gabv, steps=5, fold_clip=True):
     ref = torch.nn.parallel.DistributedDataParallel(a, device_ids=[dev.index], bucket_cap_mb=0.008,
                                                     gradient_as_bucket_view=gabv)
     ours = ddp_b200.DistributedDataParallel(b, device_ids=[dev.index], bucket_cap_mb=0.008,
-                                            gradient_as_bucket_view=gabv)
+                                            gradient_as_bucket_view=gabv, fused_allreduce=fused)
     o_ref = torch.optim.AdamW(a.parameters(), lr=1e-2, fused=True)
     o_our = ddp_b200.AdamW(b.parameters(), lr=1e-2)
     for s in range(steps):
@@ -126,7 +126,53 @@ def _two_rank_worker(rank, ws, port):
     for dtype in (torch.float32, torch.bfloat16):
         for gabv in (False, True):
             _train_compare(rank, ws, dtype, gabv)
+    # the same steps with the bucket allreduce + norm done by the fused peer-memory kernel,
+    # through NVLink peer loads/stores and through NVSwitch multicast
+    for mode in ("peer", "mc"):
+        os.environ["DDPB200_FUSED_MODE"] = mode
+        for dtype in (torch.float32, torch.bfloat16):
+            for gabv in (False, True):
+                _train_compare(rank, ws, dtype, gabv, fused=True)
+        _fused_vs_nccl(rank, ws, mode)
     dist.destroy_process_group()
+
+
+def _fused_vs_nccl(rank, ws, mode):
+    """Fused allreduce+norm on ragged segments against NCCL + a separate norm: sums within one
+    rounding of the bucket dtype, identical bits on every rank, sums of squares of exactly what was
+    stored."""
+    import ddp_b200
+    from ddp_b200.symm import SymmetricArena
+    dev = torch.device("cuda", rank)
+    K = ddp_b200.CudaKernels()
+    sizes = [5, 4096, 70001, 2047, 1 << 20, 0, 33]
+    starts, o = [], 0
+    for n in sizes:                    # segments back to back (no padding): some land misaligned
+        starts.append(o)
+        o += n
+    for dt in (torch.bfloat16, torch.float32):
+        arena = SymmetricArena(o, dt, dev, dist.group.WORLD, max_chunks=o // 2048 + len(sizes) + 1)
+        g = torch.Generator(device=dev).manual_seed(7 + rank)
+        arena.tensor.normal_(0, 0.01, generator=g)
+        ref = arena.tensor.clone()
+        dist.all_reduce(ref)
+        views = [arena.tensor[s:s + n] for s, n in zip(starts, sizes)]
+        tab = K.table([None, views, None, None], sizes, chunk_elems=2048, device=dev)
+        ss = torch.empty(len(sizes), dtype=torch.float32, device=dev)
+        K.allreduce_sumsq(tab, dt, arena, ss)
+        torch.cuda.synchronize()
+        got = arena.tensor.clone()
+        tol = dict(rtol=2 ** -7, atol=1e-6) if dt == torch.bfloat16 else dict(rtol=1e-6, atol=1e-9)
+        assert torch.allclose(got.float(), ref.float(), **tol), (mode, dt)
+        want_ss = torch.stack([v.double().pow(2).sum() for v in views]).float()
+        assert torch.allclose(ss, want_ss, rtol=3e-6, atol=0), (mode, dt, ss, want_ss)
+        both = [torch.empty_like(got) for _ in range(ws)]
+        dist.all_gather(both, got)
+        assert torch.equal(both[0], both[1]), "ranks hold different averaged gradients"
+        ss_all = [torch.empty_like(ss) for _ in range(ws)]
+        dist.all_gather(ss_all, ss)
+        assert torch.equal(ss_all[0], ss_all[1]), "ranks hold different norms"
+        del arena
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (gpurun --gpus 2)")
