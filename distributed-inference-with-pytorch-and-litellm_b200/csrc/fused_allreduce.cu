@@ -17,6 +17,7 @@
 // multicast mode (1 + 1/n) * S. Multicast wins from 4 ranks up; at 2 ranks peer mode moves less.
 // The arena must be symmetric memory (same offset on every rank); the caller provides the barriers
 // (all ranks packed before this kernel; all ranks finished it before anyone reads the arena).
+#include <stdlib.h>
 #include "launch.cuh"
 
 namespace ddpb200 {
@@ -55,9 +56,10 @@ template <int DT> __device__ __forceinline__ void unpack128(const Raw<4>& t, flo
   }
 }
 
-// MC: 1 = multicast (multimem) for the vector body, 0 = peer loads/stores.
-template <int DT, int MC>
-__global__ void __launch_bounds__(kThreads, 2)
+// MC: 1 = multicast (multimem) for the vector body, 0 = peer loads/stores. W: compile-time bound on
+// the world size (2, 4 or 8), so that a 2-rank job does not carry registers for 8 peers.
+template <int DT, int MC, int W>
+__global__ void __launch_bounds__(kThreads, (MC || W <= 2) ? 3 : 2)
 fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, const __grid_constant__ PeerMap pm) {
   constexpr int ES = ElemOf<DT>::size;
   constexpr int G = 32 / ES;            // 256-bit groups in peer mode
@@ -94,15 +96,15 @@ fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, 
       const int64_t groups_end = len / G * G;
 #pragma unroll 1
       for (int64_t i = (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
-        Raw<8> raw[DDPB200_MAX_PEERS];
+        Raw<8> raw[W];
 #pragma unroll
-        for (int p = 0; p < DDPB200_MAX_PEERS; ++p)                       // all loads in flight first
+        for (int p = 0; p < W; ++p)                                        // all loads in flight first
           if (p < world) raw[p] = ldg256(pm.arena[p] + off + i * ES);
         float sum[G];
 #pragma unroll
         for (int k = 0; k < G; ++k) sum[k] = 0.f;
 #pragma unroll
-        for (int p = 0; p < DDPB200_MAX_PEERS; ++p)
+        for (int p = 0; p < W; ++p)
           if (p < world) {                                                 // rank order: same bits everywhere
             if constexpr (DT == DDPB200_F32) {
 #pragma unroll
@@ -129,7 +131,7 @@ fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, 
           }
         }
 #pragma unroll
-        for (int p = 0; p < DDPB200_MAX_PEERS; ++p)
+        for (int p = 0; p < W; ++p)
           if (p < world) stg256(pm.arena[p] + off + i * ES, out);
       }
       done = groups_end;
@@ -194,19 +196,27 @@ extern "C" DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev
   const int sms = sm_count_cached(&err);
   if (err) return err;
   const int64_t mine = (total_chunks - pm.rank + pm.world - 1) / pm.world;     // chunks this rank owns
-  const int64_t cap = (int64_t)sms * 2;
+  static const int env_ctas = [] { const char* e = getenv("DDPB200_AR_CTAS"); return e ? atoi(e) : 0; }();
+  // measured at 2 ranks (profiles/r01_arbench.txt): peer mode is NVLink-bound from 1 CTA/SM (3.71 ms vs 3.79 at 2)
+  const int ctas = env_ctas > 0 ? env_ctas : (use_multicast ? 2 : 1);
+  const int64_t cap = (int64_t)sms * ctas;
   const int grid = (int)(mine < cap ? (mine > 0 ? mine : 1) : cap);
   DevTable tab{dev_table, (int)n};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define DDPB200_AR_LAUNCH(DT, MCV, WV)                                                                \
+  fused_allreduce_kernel<DT, MCV, WV><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm)
 #define DDPB200_AR_CASE(DT)                                                                          \
   if (dtype == DT) {                                                                                 \
-    if (use_multicast) fused_allreduce_kernel<DT, 1><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm); \
-    else fused_allreduce_kernel<DT, 0><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm);                \
+    if (use_multicast) DDPB200_AR_LAUNCH(DT, 1, 2);                                                  \
+    else if (pm.world <= 2) DDPB200_AR_LAUNCH(DT, 0, 2);                                             \
+    else if (pm.world <= 4) DDPB200_AR_LAUNCH(DT, 0, 4);                                             \
+    else DDPB200_AR_LAUNCH(DT, 0, 8);                                                                \
     return (int)cudaGetLastError();                                                                  \
   }
   DDPB200_AR_CASE(DDPB200_BF16)
   DDPB200_AR_CASE(DDPB200_F32)
 #undef DDPB200_AR_CASE
+#undef DDPB200_AR_LAUNCH
   return DDPB200_E_UNSUPPORTED;
 }
 

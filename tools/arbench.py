@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""Gradient-collective microbench (tuning aid): on the Llama-3.2-1B bucket arena (2.47 GB bf16), times
+NCCL allreduce (+ the separate norm launch it needs) against the fused peer-memory allreduce+norm
+kernel in peer and multicast mode. Launch with torchrun, one rank per GPU."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+
+import bench
+import ddp_b200
+from ddp_b200.symm import SymmetricArena
+
+
+def main():
+    rank, ws, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=ws, device_id=dev)
+    K = ddp_b200.CudaKernels()
+    shapes = bench.llama_param_shapes(**bench.WORKLOADS["llama-3.2-1b"])
+    numel = [int(torch.Size(s).numel()) for s in shapes]
+    n = sum(numel)
+    arena = SymmetricArena(n, torch.bfloat16, dev, dist.group.WORLD, max_chunks=n // 2048 + len(numel) + 1)
+    arena.tensor.normal_(0, 0.01)
+    views, o = [], 0
+    for k in numel:
+        views.append(arena.tensor[o:o + k])
+        o += k
+    tab = K.table([None, views, None, None], numel, device=dev)
+    ss = torch.empty(len(numel), dtype=torch.float32, device=dev)
+    S = n * 2
+
+    def timed(fn, reps=5):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record(); torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / reps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    def nccl():
+        dist.all_reduce(arena.tensor)
+        K.sumsq(tab, torch.bfloat16, ss)
+
+    res = {"world": ws, "bytes": S, "ar_ctas": os.environ.get("DDPB200_AR_CTAS", "2")}
+    ms = timed(nccl)
+    res["nccl+norm"] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws)
+    ms = timed(lambda: dist.all_reduce(arena.tensor))
+    res["nccl"] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws)
+    for mode in ("peer", "mc"):
+        if mode == "mc" and not arena.multicast:
+            continue
+        arena.use_multicast = mode == "mc"
+        arena.tensor.normal_(0, 0.01)
+        ms = timed(lambda: K.allreduce_sumsq(tab, torch.bfloat16, arena, ss))
+        res[f"fused-{mode}"] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws)
+    if rank == 0:
+        print(json.dumps(res))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,61 @@
+#!/usr/bin/env python
+"""Correctness of the fused peer-memory allreduce+norm at any world size (torchrun, one rank per GPU):
+against NCCL's allreduce within one rounding of the bucket dtype, identical bits on all ranks, sums of
+squares of exactly what was stored. Prints FUSED_CHECK_OK on rank 0."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+
+import ddp_b200
+from ddp_b200.symm import SymmetricArena
+
+
+def main():
+    rank, ws, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=ws, device_id=dev)
+    K = ddp_b200.CudaKernels()
+    sizes = [5, 4096, 70001, 2047, 1 << 22, 0, 33, 1 << 20]
+    starts, o = [], 0
+    for n in sizes:
+        starts.append(o)
+        o += n
+    for dt in (torch.bfloat16, torch.float32):
+        arena = SymmetricArena(o, dt, dev, dist.group.WORLD, max_chunks=o // 2048 + len(sizes) + 1)
+        views = [arena.tensor[s:s + n] for s, n in zip(starts, sizes)]
+        tab = K.table([None, views, None, None], sizes, chunk_elems=2048, device=dev)
+        for mode in ("peer", "mc"):
+            if mode == "mc" and not arena.multicast:
+                continue
+            arena.use_multicast = mode == "mc"
+            g = torch.Generator(device=dev).manual_seed(7 + rank)
+            arena.tensor.normal_(0, 0.01, generator=g)
+            ref = arena.tensor.clone()
+            dist.all_reduce(ref)
+            ss = torch.empty(len(sizes), dtype=torch.float32, device=dev)
+            K.allreduce_sumsq(tab, dt, arena, ss)
+            torch.cuda.synchronize()
+            got = arena.tensor.clone()
+            tol = dict(rtol=2 ** -6, atol=1e-5) if dt == torch.bfloat16 else dict(rtol=2e-6, atol=1e-8)
+            assert torch.allclose(got.float(), ref.float(), **tol), (mode, dt, float((got.float() - ref.float()).abs().max()))
+            want = torch.stack([v.double().pow(2).sum() for v in views]).float()
+            assert torch.allclose(ss, want, rtol=3e-6, atol=0), (mode, dt)
+            allg = [torch.empty_like(got) for _ in range(ws)]
+            dist.all_gather(allg, got)
+            assert all(torch.equal(allg[0], x) for x in allg[1:]), "ranks differ"
+            alls = [torch.empty_like(ss) for _ in range(ws)]
+            dist.all_gather(alls, ss)
+            assert all(torch.equal(alls[0], x) for x in alls[1:]), "norms differ"
+        del arena
+    if rank == 0:
+        print("FUSED_CHECK_OK world", ws)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
