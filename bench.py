@@ -124,7 +124,7 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                          "--format=csv,noheader,nounits", "-lms", "25"], stdout=self.f,
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -202,8 +202,17 @@ def run_ours(args):
     numel = [p.numel() for p in params]
     total = sum(numel)
     esize = 2
-    ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
-                                           fused_allreduce=(args.allreduce == "fused"))
+    fused_note = None
+    try:
+        ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
+                                               fused_allreduce=(args.allreduce == "fused"))
+    except Exception as e:          # symmetric memory could not be set up on this box: say so, use NCCL
+        if args.allreduce != "fused":
+            raise
+        fused_note = f"fused allreduce unavailable ({type(e).__name__}: {str(e)[:120]}); NCCL used"
+        print(fused_note, file=sys.stderr, flush=True)
+        ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
+                                               fused_allreduce=False)
     opt = ddp_b200.AdamW(params, lr=LR, weight_decay=1e-2)
 
     # synthetic gradients, resident in HBM, one tensor per parameter (rank-dependent values)
@@ -234,15 +243,15 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     step(first=True)                    # iteration 0: one bucket, records the ready order
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()                  # samples the same load from the warm-up on, through the timed region
     for _ in range(max(args.warmup, 3)):
         step()                          # rebuilt buckets from here on
     stats0 = dict(ddp._get_ddp_logging_data())
 
     # ---- timed: inputs resident in HBM -----------------------------------------------------------
-    clocks = ClockSampler(local)
     sync_all()
-    if rank == 0:
-        clocks.start()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     for i in range(args.steps):
@@ -348,7 +357,8 @@ def run_ours(args):
             "gpu_launches": launches,
             "nccl_allreduces": 0 if ddp._fused else allreduces,
             "fused_allreduces": stats1.get("fused_allreduces", 0) - stats0.get("fused_allreduces", 0),
-            "allreduce_impl": "fused peer-memory kernel" if ddp._fused else ("nccl" if ws > 1 else "none"),
+            "allreduce_impl": ("fused peer-memory kernel (" + ("multicast" if any(a.use_multicast for a in ddp._sym.values()) else "peer") + ")")
+                              if ddp._fused else ((fused_note or "nccl") if ws > 1 else "none"),
             "roofline": {"kernel": "adamw_kernel (fused clip+AdamW, bf16)", "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                          "frac_of_8000_nominal": achieved / 8000.0, "algorithmic_bytes_per_launch": alg_bytes,
@@ -487,12 +497,12 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=list(WORKLOADS), default="llama-3.2-1b")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--allreduce", choices=["nccl", "fused"], default=os.environ.get("DDPB200_BENCH_ALLREDUCE", "nccl"),
+    ap.add_argument("--allreduce", choices=["nccl", "fused"], default=os.environ.get("DDPB200_BENCH_ALLREDUCE", "fused"),
                     help="N>1: NCCL allreduce + norm launch, or the fused peer-memory allreduce+norm kernel")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -156,6 +156,7 @@ class DistributedDataParallel(nn.Module):
         self._next_bucket = 0
         self._sumsq_valid = False
         self._coalesce = False
+        self._coalesce_groups = int(os.environ.get("DDPB200_COALESCE_GROUPS", "4"))
         self._stats = {"iterations": 0, "pack_launches": 0, "allreduces": 0, "norm_launches": 0,
                        "unpack_launches": 0, "rebuilt_bucket_sizes": []}
 
@@ -427,12 +428,18 @@ class DistributedDataParallel(nn.Module):
         (or unpack+norm) launch. Not used from autograd hooks, where ranks could disagree on which
         buckets happen to be complete together."""
         k = self._kernels
+        # Up to `_coalesce_groups` sub-runs of about equal size: the pack of sub-run g+1 (HBM-bound,
+        # compute stream) overlaps the collective of sub-run g (NVLink-bound, side stream).
+        total = sum(bk.spec.numel for bk in self._buckets[b0:b1])
+        budget = max(1, -(-total // max(1, self._coalesce_groups)))
         i = b0
         while i < b1:
             j = i
             dt = self._buckets[i].dtype
             grads = []
-            while j < b1 and self._buckets[j].dtype == dt:
+            taken = 0
+            while j < b1 and self._buckets[j].dtype == dt and (taken == 0 or taken + self._buckets[j].spec.numel <= budget):
+                taken += self._buckets[j].spec.numel
                 for p in self._buckets[j].params:
                     g = p.grad
                     if g is None:

@@ -162,7 +162,8 @@ def _fused_vs_nccl(rank, ws, mode):
         K.allreduce_sumsq(tab, dt, arena, ss)
         torch.cuda.synchronize()
         got = arena.tensor.clone()
-        tol = dict(rtol=2 ** -7, atol=1e-6) if dt == torch.bfloat16 else dict(rtol=1e-6, atol=1e-9)
+        # NCCL rounds to the bucket dtype at every hop; tolerance in units of the TERMS' size (~0.03)
+        tol = dict(rtol=2 ** -7, atol=5e-4) if dt == torch.bfloat16 else dict(rtol=1e-6, atol=1e-8)
         assert torch.allclose(got.float(), ref.float(), **tol), (mode, dt)
         want_ss = torch.stack([v.double().pow(2).sum() for v in views]).float()
         assert torch.allclose(ss, want_ss, rtol=3e-6, atol=0), (mode, dt, ss, want_ss)
