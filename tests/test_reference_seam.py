@@ -45,3 +45,21 @@ def test_script_runs_two_ranks_on_cpu():
     res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stderr[-2000:]
     assert "done: 3 steps" in res.stderr
+
+
+def test_gpt2_small_two_ranks_cpu_gloo():
+    """BASELINE.json configs[0]: GPT-2 small (124 M, random init) DDP fine-tune on the small synthetic
+    dataset, CPU/gloo, world_size 2 — the plumbing case. Two steps through the launch line."""
+    env = dict(os.environ, DDPB200_MODEL="gpt2", DDPB200_MAX_STEPS="2", DDPB200_SEQ_LEN="32", CUDA_VISIBLE_DEVICES="",
+               OMP_NUM_THREADS="4")
+    env.pop("MASTER_ADDR", None)
+    env.pop("MASTER_PORT", None)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29735", os.path.join(ROOT, "src", "distributed_finetuning.py")]
+    res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert "done: 2 steps" in res.stderr
+    # a random-init GPT-2 starts near ln(50257) = 10.8
+    import re
+    m = re.search(r"step 1 loss ([0-9.]+)", res.stderr)
+    assert m and 9.5 < float(m.group(1)) < 12.0, res.stderr[-500:]
