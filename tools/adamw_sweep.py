@@ -31,6 +31,62 @@ def timeit(fn, reps=10, warm=3):
     return a.elapsed_time(b) / reps
 
 
+def run_case(K, dev, peak, name, numel):
+    n = sum(numel)
+    gen = torch.Generator(device=dev).manual_seed(0)
+    p = torch.empty(n, dtype=torch.float32, device=dev).normal_(0, 0.02, generator=gen)
+    g = torch.empty(n, dtype=torch.float32, device=dev).normal_(0, 0.01, generator=gen)
+    m = torch.zeros(n, dtype=torch.float32, device=dev)
+    v = torch.zeros(n, dtype=torch.float32, device=dev)
+
+    def views(t):
+        o, r = 0, []
+        for k in numel:
+            r.append(t[o:o + k])
+            o += k
+        return r
+
+    tab = K.table([views(p), views(g), views(m), views(v)], numel, device=dev)
+    ss = torch.empty(len(numel), dtype=torch.float32, device=dev)
+    hp = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
+    step = [0]
+
+    def ours():
+        step[0] += 1
+        K.sumsq(tab, torch.float32, ss)
+        coef = K.norm_finalize(ss, 1.0, False)
+        K.adamw(tab, torch.float32, torch.float32, torch.float32, step=step[0], clip_coef=coef[1:2], **hp)
+
+    def ours_adam_only():
+        step[0] += 1
+        K.adamw(tab, torch.float32, torch.float32, torch.float32, step=step[0], **hp)
+
+    t_ours = timeit(ours)
+    t_adam = timeit(ours_adam_only)
+    del tab, m, v                     # torch's optimizer allocates its own state: make room (8 B: 64 GB)
+    gc.collect()
+    torch.cuda.empty_cache()
+    ps = [torch.nn.Parameter(x) for x in views(p)]
+    for q, gg in zip(ps, views(g)):
+        q.grad = gg
+    opt = torch.optim.AdamW(ps, lr=1e-3, fused=True)
+    # note: torch's clip scales grads in place; restore is unnecessary for timing
+    t_torch_adam = timeit(opt.step)
+
+    def torch_both():
+        torch.nn.utils.clip_grad_norm_(ps, 1.0)
+        opt.step()
+
+    t_torch = timeit(torch_both)
+    r = dict(case=name, params=n, tensors=len(numel),
+             ours_adamw_ms=t_adam, ours_adamw_gbs=28 * n / t_adam / 1e6, ours_adamw_frac_of_measured_peak=28 * n / t_adam / 1e6 / peak,
+             ours_adamw_frac_of_8000=28 * n / t_adam / 1e6 / 8000,
+             torch_fused_adamw_ms=t_torch_adam, torch_fused_adamw_gbs=28 * n / t_torch_adam / 1e6,
+             ours_norm_clip_adamw_ms=t_ours, ours_path_gbs=32 * n / t_ours / 1e6,
+             torch_clip_plus_fused_adamw_ms=t_torch, speedup_adamw=t_torch_adam / t_adam, speedup_path=t_torch / t_ours)
+    return r
+
+
 def main():
     dev = torch.device("cuda", 0)
     K = ddp_b200.CudaKernels()
@@ -39,60 +95,12 @@ def main():
              ("flat 1B", [1_000_000_000]), ("flat 8B", [8_000_000_000]),
              ("llama-3.1-8b list (291 tensors)",
               [int(torch.Size(s).numel()) for s in bench.llama_param_shapes(**bench.WORKLOADS["llama-3.1-8b"])])]
-    out = []
+    only = os.environ.get("SWEEP_ONLY", "")
     for name, numel in cases:
-        n = sum(numel)
-        gen = torch.Generator(device=dev).manual_seed(0)
-        p = torch.empty(n, dtype=torch.float32, device=dev).normal_(0, 0.02, generator=gen)
-        g = torch.empty(n, dtype=torch.float32, device=dev).normal_(0, 0.01, generator=gen)
-        m = torch.zeros(n, dtype=torch.float32, device=dev)
-        v = torch.zeros(n, dtype=torch.float32, device=dev)
-
-        def views(t):
-            o, r = 0, []
-            for k in numel:
-                r.append(t[o:o + k])
-                o += k
-            return r
-
-        tab = K.table([views(p), views(g), views(m), views(v)], numel, device=dev)
-        ss = torch.empty(len(numel), dtype=torch.float32, device=dev)
-        hp = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
-        step = [0]
-
-        def ours():
-            step[0] += 1
-            K.sumsq(tab, torch.float32, ss)
-            coef = K.norm_finalize(ss, 1.0, False)
-            K.adamw(tab, torch.float32, torch.float32, torch.float32, step=step[0], clip_coef=coef[1:2], **hp)
-
-        def ours_adam_only():
-            step[0] += 1
-            K.adamw(tab, torch.float32, torch.float32, torch.float32, step=step[0], **hp)
-
-        t_ours = timeit(ours)
-        t_adam = timeit(ours_adam_only)
-        ps = [torch.nn.Parameter(x) for x in views(p)]
-        for q, gg in zip(ps, views(g)):
-            q.grad = gg
-        opt = torch.optim.AdamW(ps, lr=1e-3, fused=True)
-        # note: torch's clip scales grads in place; restore is unnecessary for timing
-        t_torch_adam = timeit(opt.step)
-
-        def torch_both():
-            torch.nn.utils.clip_grad_norm_(ps, 1.0)
-            opt.step()
-
-        t_torch = timeit(torch_both)
-        r = dict(case=name, params=n, tensors=len(numel),
-                 ours_adamw_ms=t_adam, ours_adamw_gbs=28 * n / t_adam / 1e6, ours_adamw_frac_of_measured_peak=28 * n / t_adam / 1e6 / peak,
-                 ours_adamw_frac_of_8000=28 * n / t_adam / 1e6 / 8000,
-                 torch_fused_adamw_ms=t_torch_adam, torch_fused_adamw_gbs=28 * n / t_torch_adam / 1e6,
-                 ours_norm_clip_adamw_ms=t_ours, ours_path_gbs=32 * n / t_ours / 1e6,
-                 torch_clip_plus_fused_adamw_ms=t_torch, speedup_adamw=t_torch_adam / t_adam, speedup_path=t_torch / t_ours)
+        if only and only not in name:
+            continue
+        r = run_case(K, dev, peak, name, numel)     # a function, so that every tensor of a case dies with it
         print(json.dumps(r), flush=True)
-        out.append(r)
-        del opt, ps, tab, p, g, m, v
         gc.collect()
         torch.cuda.empty_cache()
 
