@@ -203,17 +203,22 @@ def run_ours(args):
     total = sum(numel)
     esize = 2
     fused_note = None
+    zero1 = bool(args.zero1) and ws > 1
     try:
         ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
-                                               fused_allreduce=(args.allreduce == "fused"))
+                                               fused_allreduce=(args.allreduce == "fused" or zero1),
+                                               shard_optimizer=zero1)
     except Exception as e:          # symmetric memory could not be set up on this box: say so, use NCCL
-        if args.allreduce != "fused":
+        if args.allreduce != "fused" or zero1:
             raise
         fused_note = f"fused allreduce unavailable ({type(e).__name__}: {str(e)[:120]}); NCCL used"
         print(fused_note, file=sys.stderr, flush=True)
         ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
                                                fused_allreduce=False)
-    opt = ddp_b200.AdamW(params, lr=LR, weight_decay=1e-2)
+    if zero1:
+        opt = ddp_b200.ShardedAdamW(ddp, lr=LR, weight_decay=1e-2)
+    else:
+        opt = ddp_b200.AdamW(params, lr=LR, weight_decay=1e-2)
 
     # synthetic gradients, resident in HBM, one tensor per parameter (rank-dependent values)
     gflat = torch.empty(total, dtype=dtype, device=dev).normal_(0, 0.01, generator=torch.Generator(device=dev).manual_seed(1 + rank))
@@ -335,20 +340,20 @@ def run_ours(args):
     out = None
     if rank == 0:
         peak, peak_src = measured_peaks()
-        alg_bytes = 14 * total                                       # bf16 p,g,m,v read + p,m,v write
+        alg_bytes = 14 * total // (ws if zero1 else 1)                # bf16 p,g,m,v read + p,m,v write (1/ws of them if sharded)
         achieved = alg_bytes / (adamw_ms * 1e-3) / 1e9
         bucket_bytes = stats1["bucket_sizes"]
         out = {
             "metric": METRIC, "value": ws * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ws,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic", "impl": "ours",
+            "data": "synthetic", "impl": "ours" + ("-zero1" if zero1 else ""),
             "config": {"workload": f"{args.workload}-arch parameter set, bf16 p/g/m/v, {len(params)} tensors, "
                                    f"{total} elements; gradient_as_bucket_view, 25 MiB buckets "
                                    f"({len(bucket_bytes)} after rebuild), max_norm {MAX_NORM}, AdamW lr {LR}",
                        "global_batch": f"{ws} replicas x 1 synthetic gradient set",
                        "l2": "working set per step 12.4 GB >> 126 MB L2; no flush needed",
-                       "parallelism": f"dp{ws}"},
+                       "parallelism": f"dp{ws}" + (" + sharded optimizer (ZeRO-1 style)" if zero1 else "")},
             "steps_per_s": args.steps / (ms * 1e-3),
             "e2e": {"value": ws * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "steps": e2e_steps,
                     "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8,
@@ -502,6 +507,9 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=list(WORKLOADS), default="llama-3.2-1b")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--zero1", action="store_true",
+                    help="N>1: the sharded update (reduce-scatter + AdamW on owned chunks + all-gather of parameters) "
+                         "instead of the drop-in replicated path; an extension, not the default")
     ap.add_argument("--allreduce", choices=["nccl", "fused"], default=os.environ.get("DDPB200_BENCH_ALLREDUCE", "fused"),
                     help="N>1: NCCL allreduce + norm launch, or the fused peer-memory allreduce+norm kernel")
     args = ap.parse_args()

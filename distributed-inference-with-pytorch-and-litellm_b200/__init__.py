@@ -13,9 +13,10 @@ from .clip import clip_grad_norm_
 from .ddp import DistributedDataParallel, GradBucket
 from .kernels import CudaKernels, SegTable, default_kernels
 from .optim import AdamW
+from .zero import ShardedAdamW
 
 DDP = DistributedDataParallel
 
-__all__ = ["DistributedDataParallel", "DDP", "GradBucket", "AdamW", "clip_grad_norm_",
+__all__ = ["DistributedDataParallel", "DDP", "GradBucket", "AdamW", "ShardedAdamW", "clip_grad_norm_",
            "compute_bucket_assignment_by_size", "layout_buckets", "CudaKernels", "SegTable",
            "default_kernels", "build_native"]

@@ -59,6 +59,9 @@ SIGNATURES = {
     "ddpb200_adamw_bias_corrections": (ctypes.c_int, [_f64, _f64, _i64, _vp]),
     "ddpb200_allreduce_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _vp]),
     "ddpb200_fold_chunk_partials": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
+    "ddpb200_reduce_scatter_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _vp]),
+    "ddpb200_sharded_adamw_allgather": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _f64, _vp,
+                                                       _f64, _f64, _f64, _f64, _i64, _vp, _u32, _i32, _vp]),
 }
 
 

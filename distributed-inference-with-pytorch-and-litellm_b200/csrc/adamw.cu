@@ -19,46 +19,9 @@
 #include <math.h>
 #include <stdlib.h>
 #include "launch.cuh"
+#include "adamw_math.cuh"
 
 namespace ddpb200 {
-
-struct AdamScalars {
-  float lr, beta1, beta2, eps, weight_decay, bc1, bc2_sqrt, rcp_bc2_sqrt;
-};
-
-// MODE: how the per-launch options reach the element function
-constexpr int kModeGeneral  = 0;  // runtime flags (grad_scale, maximize, store-grad, wd==0, unrounded clip)
-constexpr int kModeFastClip = 1;  // clip * round-to-grad-dtype, weight decay on, nothing else
-constexpr int kModeFastPlain = 2; // no clip, weight decay on, nothing else
-
-struct AdamRuntime {
-  float lr_wd, step_size, grad_scale, clip;
-  bool has_scale, has_clip, round_clip, maximize, has_wd;
-};
-
-template <int GDT, int MODE>
-__device__ __forceinline__ void adamw_elem(float& p, float& g, float& m, float& v, const AdamScalars& a,
-                                           const AdamRuntime& r) {
-  float gm;
-  if constexpr (MODE == kModeGeneral) {
-    if (r.has_scale) g = __fdiv_rn(g, r.grad_scale);
-    if (r.has_clip) {
-      g = __fmul_rn(g, r.clip);
-      if (r.round_clip) g = round_through<GDT>(g);
-    }
-    gm = r.maximize ? -g : g;
-    if (r.has_wd) p = __fmaf_rn(-r.lr_wd, p, p);
-  } else {
-    if constexpr (MODE == kModeFastClip) g = round_through<GDT>(__fmul_rn(g, r.clip));
-    gm = g;
-    p = __fmaf_rn(-r.lr_wd, p, p);                                   // p -= lr*wd*p
-  }
-  m = __fmaf_rn(a.beta1, m, __fmaf_rn(-a.beta1, gm, gm));            // lerp(m, g, 1-b1)
-  const float gg = __fmul_rn(gm, gm);
-  v = __fmaf_rn(a.beta2, v, __fmaf_rn(-a.beta2, gg, gg));
-  const float denom = __fadd_rn(div_by_const(__fsqrt_rn(v), a.bc2_sqrt, a.rcp_bc2_sqrt), a.eps);
-  p = __fsub_rn(p, __fdiv_rn(__fmul_rn(r.step_size, m), denom));
-}
 
 // One chunk through G-element groups (vector accesses); returns how many elements were done, the
 // ragged end is left to the caller's scalar loop.
@@ -99,17 +62,7 @@ adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chun
              uint32_t flags) {
   constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
   if (found_inf_ptr && __ldg(found_inf_ptr) == 1.0f) return;      // GradScaler skip (cuh:137-139)
-  if (lr_ptr) a.lr = __ldg(lr_ptr);
-  AdamRuntime r;
-  r.lr_wd = __fmul_rn(a.lr, a.weight_decay);
-  r.step_size = __fdiv_rn(a.lr, a.bc1);
-  r.has_scale = grad_scale_ptr != nullptr;
-  r.grad_scale = r.has_scale ? __ldg(grad_scale_ptr) : 1.f;
-  r.has_clip = clip_ptr != nullptr;
-  r.clip = r.has_clip ? __ldg(clip_ptr) : 1.f;
-  r.round_clip = (flags & DDPB200_ADAMW_ROUND_CLIPPED_GRAD) != 0;
-  r.maximize = (flags & DDPB200_ADAMW_MAXIMIZE) != 0;
-  r.has_wd = a.weight_decay != 0.f;
+  const AdamRuntime r = make_adam_runtime(a, lr_ptr, clip_ptr, grad_scale_ptr, flags);
   const bool store_g = (flags & DDPB200_ADAMW_STORE_GRAD) != 0;
   const int64_t chunk_base = tab.begin(0);
 
@@ -193,10 +146,7 @@ extern "C" DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, in
   if (n == 0) return 0;
   float bc[2];
   ddpb200_adamw_bias_corrections(beta1, beta2, step, bc);
-  AdamScalars a;
-  a.lr = (float)lr; a.beta1 = (float)beta1; a.beta2 = (float)beta2; a.eps = (float)eps;
-  a.weight_decay = (float)weight_decay;
-  a.bc1 = bc[0]; a.bc2_sqrt = bc[1]; a.rcp_bc2_sqrt = 1.0f / bc[1];   // IEEE: correctly rounded
+  AdamScalars a = make_adam_scalars(lr, beta1, beta2, eps, weight_decay, bc);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // common cases get compile-time options; anything else takes the general kernel
   int mode = kModeGeneral;

@@ -19,32 +19,9 @@
 // (all ranks packed before this kernel; all ranks finished it before anyone reads the arena).
 #include <stdlib.h>
 #include "launch.cuh"
+#include "peer.cuh"
 
 namespace ddpb200 {
-
-struct PeerMap {                        // device-side copy of ddpb200_peer_map
-  char* arena[DDPB200_MAX_PEERS];
-  float* partials[DDPB200_MAX_PEERS];
-  char* mc;
-  int rank, world;
-};
-
-__device__ __forceinline__ Raw<4> mc_ld_reduce_bf16x8(const void* p) {
-  Raw<4> x;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-               : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]) : "l"(__cvta_generic_to_global(p)) : "memory");
-  return x;
-}
-__device__ __forceinline__ Raw<4> mc_ld_reduce_f32x4(const void* p) {
-  Raw<4> x;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]) : "l"(__cvta_generic_to_global(p)) : "memory");
-  return x;
-}
-__device__ __forceinline__ void mc_st_128(void* p, const Raw<4>& x) {
-  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
-               :: "l"(__cvta_generic_to_global(p)), "r"(x.r[0]), "r"(x.r[1]), "r"(x.r[2]), "r"(x.r[3]) : "memory");
-}
 
 template <int DT> __device__ __forceinline__ void unpack128(const Raw<4>& t, float (&v)[16 / ElemOf<DT>::size]) {
   if constexpr (DT == DDPB200_F32) {
@@ -58,7 +35,11 @@ template <int DT> __device__ __forceinline__ void unpack128(const Raw<4>& t, flo
 
 // MC: 1 = multicast (multimem) for the vector body, 0 = peer loads/stores. W: compile-time bound on
 // the world size (2, 4 or 8), so that a 2-rank job does not carry registers for 8 peers.
-template <int DT, int MC, int W>
+// SCATTER: the owner keeps the reduced chunk to itself (local store only): the reduce-scatter half, for
+// the sharded update (sharded_update.cu) which sends updated PARAMETERS back instead of gradients.
+// A chunk's owner is (absolute chunk id) % world, so ownership does not depend on how a step slices
+// the table into launches.
+template <int DT, int MC, int W, bool SCATTER>
 __global__ void __launch_bounds__(kThreads, (MC || W <= 2) ? 3 : 2)
 fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, const __grid_constant__ PeerMap pm) {
   constexpr int ES = ElemOf<DT>::size;
@@ -69,7 +50,8 @@ fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, 
   const int world = pm.world;
   char* const local = pm.arena[pm.rank];
 
-  for (int64_t c = pm.rank + (int64_t)world * blockIdx.x; c < total_chunks; c += (int64_t)world * gridDim.x) {
+  const int64_t c0 = ((pm.rank - chunk_base % world) % world + world) % world;   // first relative chunk this rank owns
+  for (int64_t c = c0 + (int64_t)world * blockIdx.x; c < total_chunks; c += (int64_t)world * gridDim.x) {
     const int s = find_seg(tab, c + chunk_base);
     const int64_t start = (c + chunk_base - tab.begin(s)) * chunk_elems;
     const int64_t rest = tab.numel(s) - start;
@@ -89,7 +71,8 @@ fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, 
         unpack128<DT>(t, v);
 #pragma unroll
         for (int k = 0; k < H; ++k) acc[k & 3] = __fmaf_rn(v[k], v[k], acc[k & 3]);
-        mc_st_128(pm.mc + off + i * ES, t);
+        if constexpr (SCATTER) stg128(local + off + i * ES, t);
+        else mc_st_128(pm.mc + off + i * ES, t);
       }
       done = groups_end;
     } else if (!MC && (off % 32) == 0) {
@@ -130,9 +113,13 @@ fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, 
             acc[(2 * k + 1) & 3] = __fmaf_rn(hi, hi, acc[(2 * k + 1) & 3]);
           }
         }
+        if constexpr (SCATTER) {
+          stg256(local + off + i * ES, out);
+        } else {
 #pragma unroll
-        for (int p = 0; p < W; ++p)
-          if (p < world) stg256(pm.arena[p] + off + i * ES, out);
+          for (int p = 0; p < W; ++p)
+            if (p < world) stg256(pm.arena[p] + off + i * ES, out);
+        }
       }
       done = groups_end;
     }
@@ -142,7 +129,8 @@ fused_allreduce_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, 
       for (int p = 0; p < world; ++p) sum = __fadd_rn(sum, load1<DT>(pm.arena[p] + off, i));
       sum = round_through<DT>(sum);
       acc[0] = __fmaf_rn(sum, sum, acc[0]);
-      for (int p = 0; p < world; ++p) store1<DT>(pm.arena[p] + off, i, sum);
+      if constexpr (SCATTER) store1<DT>(local + off, i, sum);
+      else for (int p = 0; p < world; ++p) store1<DT>(pm.arena[p] + off, i, sum);
     }
 
     const float total = block_sum(__fadd_rn(__fadd_rn(acc[0], acc[1]), __fadd_rn(acc[2], acc[3])), red);
@@ -172,30 +160,21 @@ fold_partials_kernel(DevTable tab, int64_t total_chunks, const float* __restrict
 
 }  // namespace ddpb200
 
-using namespace ddpb200;
+namespace ddpb200 {
 
-extern "C" DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n,
-                                                          int64_t total_chunks, int64_t chunk_elems,
-                                                          int32_t dtype, const ddpb200_peer_map* peers,
-                                                          int32_t use_multicast, void* stream) {
+template <bool SCATTER>
+static int launch_fused_allreduce(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
+                                  int64_t chunk_elems, int32_t dtype, const ddpb200_peer_map* peers,
+                                  int32_t use_multicast, void* stream) {
   if (!valid_chunking(n, total_chunks, chunk_elems) || !dev_table || !peers) return DDPB200_E_INVALID;
-  if (peers->world < 1 || peers->world > DDPB200_MAX_PEERS || peers->rank < 0 || peers->rank >= peers->world)
-    return DDPB200_E_INVALID;
-  if (use_multicast && !peers->arena_multicast) return DDPB200_E_INVALID;
-  if (n == 0 || total_chunks == 0) return 0;
   PeerMap pm;
-  for (int p = 0; p < DDPB200_MAX_PEERS; ++p) {
-    pm.arena[p] = p < peers->world ? static_cast<char*>(peers->arena[p]) : nullptr;
-    pm.partials[p] = p < peers->world ? peers->partials[p] : nullptr;
-    if (p < peers->world && (!pm.arena[p] || !pm.partials[p])) return DDPB200_E_INVALID;
-  }
-  pm.mc = static_cast<char*>(peers->arena_multicast);
-  pm.rank = peers->rank;
-  pm.world = peers->world;
+  if (!make_peer_map(peers, true, &pm)) return DDPB200_E_INVALID;
+  if (use_multicast && !pm.mc) return DDPB200_E_INVALID;
+  if (n == 0 || total_chunks == 0) return 0;
   int err = 0;
   const int sms = sm_count_cached(&err);
   if (err) return err;
-  const int64_t mine = (total_chunks - pm.rank + pm.world - 1) / pm.world;     // chunks this rank owns
+  const int64_t mine = (total_chunks + pm.world - 1) / pm.world;                // chunks this rank owns (upper bound)
   static const int env_ctas = [] { const char* e = getenv("DDPB200_AR_CTAS"); return e ? atoi(e) : 0; }();
   // measured at 2 ranks (profiles/r01_arbench.txt): peer mode is NVLink-bound from 1 CTA/SM (3.71 ms vs 3.79 at 2)
   const int ctas = env_ctas > 0 ? env_ctas : (use_multicast ? 2 : 1);
@@ -204,7 +183,7 @@ extern "C" DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev
   DevTable tab{dev_table, (int)n};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define DDPB200_AR_LAUNCH(DT, MCV, WV)                                                                \
-  fused_allreduce_kernel<DT, MCV, WV><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm)
+  fused_allreduce_kernel<DT, MCV, WV, SCATTER><<<grid, kThreads, 0, st>>>(tab, total_chunks, chunk_elems, pm)
 #define DDPB200_AR_CASE(DT)                                                                          \
   if (dtype == DT) {                                                                                 \
     if (use_multicast) DDPB200_AR_LAUNCH(DT, 1, 2);                                                  \
@@ -218,6 +197,24 @@ extern "C" DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev
 #undef DDPB200_AR_CASE
 #undef DDPB200_AR_LAUNCH
   return DDPB200_E_UNSUPPORTED;
+}
+
+}  // namespace ddpb200
+
+using namespace ddpb200;
+
+extern "C" DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n,
+                                                          int64_t total_chunks, int64_t chunk_elems,
+                                                          int32_t dtype, const ddpb200_peer_map* peers,
+                                                          int32_t use_multicast, void* stream) {
+  return launch_fused_allreduce<false>(dev_table, n, total_chunks, chunk_elems, dtype, peers, use_multicast, stream);
+}
+
+extern "C" DDPB200_API int ddpb200_reduce_scatter_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n,
+                                                               int64_t total_chunks, int64_t chunk_elems,
+                                                               int32_t dtype, const ddpb200_peer_map* peers,
+                                                               int32_t use_multicast, void* stream) {
+  return launch_fused_allreduce<true>(dev_table, n, total_chunks, chunk_elems, dtype, peers, use_multicast, stream);
 }
 
 extern "C" DDPB200_API int ddpb200_fold_chunk_partials(const ddpb200_seg* dev_table, int64_t n,

@@ -89,7 +89,7 @@ class DistributedDataParallel(nn.Module):
                  static_graph: bool = False, delay_all_reduce_named_params=None,
                  param_to_hook_all_reduce=None, mixed_precision=None, device_mesh=None,
                  skip_all_reduce_unused_params: bool = False, *, kernels=None,
-                 fused_allreduce: Optional[bool] = None):
+                 fused_allreduce: Optional[bool] = None, shard_optimizer: bool = False):
         super().__init__()
         if find_unused_parameters:
             raise NotImplementedError("ddp_b200: find_unused_parameters=True is outside the hot path covered")
@@ -146,6 +146,14 @@ class DistributedDataParallel(nn.Module):
             fused_allreduce = os.environ.get("DDPB200_FUSED_ALLREDUCE", "0") == "1"
         self._fused = bool(fused_allreduce) and self._cuda and 1 < self.world_size <= 8
         self._sym = {}
+        # sharded update (ZeRO-1 style, see zero.py): reduce-scatter instead of allreduce, parameters
+        # re-homed into a symmetric arena so that the owners of a chunk can write them everywhere
+        self._zero = bool(shard_optimizer)
+        if self._zero and not self._fused:
+            raise RuntimeError("shard_optimizer=True needs fused_allreduce=True on 2..8 CUDA ranks of one NVLink domain")
+        if self._zero and len({p.dtype for p in self._params}) != 1:
+            raise NotImplementedError("ddp_b200 sharded update: parameters must share one dtype")
+        self._param_sym = {}
         self._comm_hook: Optional[Callable] = None
         self._comm_hook_state = None
         self._hook_handles = []
@@ -160,11 +168,22 @@ class DistributedDataParallel(nn.Module):
         self._stats = {"iterations": 0, "pack_launches": 0, "allreduces": 0, "norm_launches": 0,
                        "unpack_launches": 0, "rebuilt_bucket_sizes": []}
 
-        limits = bucketing.initial_bucket_limits(False, static_graph, self.bucket_bytes_cap,
-                                                 self.bucket_bytes_cap_default)
-        idx, lim = bucketing.compute_bucket_assignment_by_size(self._params, limits)
-        # reversed: approximate the order in which gradients become ready (distributed.py:1254-1258)
-        self._build_buckets(list(reversed(idx)), list(reversed(lim)))
+        if self._zero:
+            # optimizer state is laid out by chunk, so the bucket layout must not change once the
+            # optimizer has stepped: build the final buckets now, in reversed registration order
+            # (the order torch assumes gradients become ready), and never rebuild
+            n = len(self._params)
+            order = list(range(n - 1, -1, -1))
+            limits = bucketing.rebuild_bucket_limits(self.bucket_bytes_cap, self.bucket_bytes_cap_default)
+            idx, lim = bucketing.compute_bucket_assignment_by_size([self._params[i] for i in order], limits, None, order)
+            self._build_buckets(idx, lim)
+            self._has_rebuilt = True
+        else:
+            limits = bucketing.initial_bucket_limits(False, static_graph, self.bucket_bytes_cap,
+                                                     self.bucket_bytes_cap_default)
+            idx, lim = bucketing.compute_bucket_assignment_by_size(self._params, limits)
+            # reversed: approximate the order in which gradients become ready (distributed.py:1254-1258)
+            self._build_buckets(list(reversed(idx)), list(reversed(lim)))
 
         ref = weakref.ref(self)
         for i, p in enumerate(self._params):
@@ -266,6 +285,18 @@ class DistributedDataParallel(nn.Module):
             self._buckets.append(bk)
             self._order.extend(spec.indices)
             first += len(spec.indices)
+        if self._zero:
+            from .symm import SymmetricArena
+            self._param_sym = {dt: SymmetricArena(n_, dt, self.device, self.process_group)
+                               for dt, n_ in sorted(arena_len.items(), key=lambda kv: str(kv[0]))}
+            with torch.no_grad():
+                for bk in self._buckets:            # same layout as the gradient arena: same byte offsets
+                    pa = self._param_sym[bk.dtype].tensor
+                    for pi, o in zip(bk.spec.indices, bk.spec.offsets):
+                        p = self._params[pi]
+                        home = pa[bk.arena_start + o:bk.arena_start + o + numels[pi]].view_as(p)
+                        home.copy_(p.data)
+                        p.data = home
         n = len(self._order)
         self._slot_of = {pi: s for s, pi in enumerate(self._order)}
         self._bucket_of = {pi: bk for bk in self._buckets for pi in bk.spec.indices}
@@ -577,7 +608,8 @@ class DistributedDataParallel(nn.Module):
         one kernel over NVLink peer memory (csrc/fused_allreduce.cu), then the copy back into p.grad
         unless gradients are bucket views."""
         k = self._kernels
-        k.allreduce_sumsq(self._view_table, dt, self._sym[dt], self._sumsq[first:first + n], first=first, count=n)
+        k.allreduce_sumsq(self._view_table, dt, self._sym[dt], self._sumsq[first:first + n], first=first, count=n,
+                          scatter=self._zero)
         self._stats["fused_allreduces"] = self._stats.get("fused_allreduces", 0) + 1
         if not self.gradient_as_bucket_view:
             self._unpack_table.host["ptr"][first:first + n, 1] = [g.data_ptr() for g in grads]

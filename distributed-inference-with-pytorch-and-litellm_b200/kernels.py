@@ -232,10 +232,11 @@ class CudaKernels:
 
     # ---- fused bucket allreduce + norm over peer memory ---------------------------------------
     def allreduce_sumsq(self, tab: SegTable, dtype: torch.dtype, arena, sumsq_out: torch.Tensor,
-                        first: int = 0, count: Optional[int] = None) -> None:
+                        first: int = 0, count: Optional[int] = None, scatter: bool = False) -> None:
         """SUM over ranks of rows [first, first+count) of the symmetric bucket arena, in place on
         every rank, and their per-tensor sums of squares into sumsq_out — barrier, one kernel,
-        barrier, fold; all on the current stream."""
+        barrier, fold; all on the current stream. scatter=True: reduce-scatter only (the owner of
+        a chunk keeps the reduced values to itself), for the sharded update."""
         if tab.dev is None:
             raise RuntimeError("allreduce_sumsq needs the device-resident table of bucket views")
         ptr, _, n, chunks = tab.args(first, count, True)
@@ -244,12 +245,38 @@ class CudaKernels:
         L = _lib.lib()
         arena.barrier()                                   # every rank has packed this range
         pm = arena.peer_map(chunk_off)
-        _lib.check(L.ddpb200_allreduce_sumsq_chunks(ptr, n, chunks, tab.chunk_elems, dtype_code(dtype),
-                                                    ctypes.addressof(pm), int(arena.use_multicast), st),
-                   "ddpb200_allreduce_sumsq_chunks")
+        fn = L.ddpb200_reduce_scatter_sumsq_chunks if scatter else L.ddpb200_allreduce_sumsq_chunks
+        _lib.check(fn(ptr, n, chunks, tab.chunk_elems, dtype_code(dtype), ctypes.addressof(pm),
+                      int(arena.use_multicast), st), "ddpb200_allreduce_sumsq_chunks")
         arena.barrier()                                   # every rank has written its chunks everywhere
         _lib.check(L.ddpb200_fold_chunk_partials(ptr, n, chunks, arena.partials.data_ptr() + 4 * chunk_off,
                                                  sumsq_out.data_ptr(), st), "ddpb200_fold_chunk_partials")
+
+
+    def sharded_adamw(self, tab: SegTable, dtype: torch.dtype, grad_arena, param_arena, exp_avg_shard: torch.Tensor,
+                      exp_avg_sq_shard: torch.Tensor, *, lr, beta1: float, beta2: float, eps: float,
+                      weight_decay: float, step: int, clip_coef: Optional[torch.Tensor] = None,
+                      round_clipped: bool = True, maximize: bool = False) -> None:
+        """AdamW on the chunks this rank owns + all-gather of the new parameters (csrc/sharded_update.cu),
+        then the cross-GPU barrier after which every rank may read parameters."""
+        if tab.dev is None:
+            raise RuntimeError("sharded_adamw needs the device-resident table of gradient views")
+        ptr, _, n, chunks = tab.args(0, None, True)
+        lr_ptr = None
+        if isinstance(lr, torch.Tensor):
+            if lr.is_cuda:
+                lr_ptr, lr = lr.data_ptr(), 0.0
+            else:
+                lr = float(lr)
+        flags = (_lib.ADAMW_ROUND_CLIPPED_GRAD if round_clipped else 0) | (_lib.ADAMW_MAXIMIZE if maximize else 0)
+        pm = param_arena.peer_map(0)
+        rc = _lib.lib().ddpb200_sharded_adamw_allgather(
+            ptr, n, chunks, tab.chunk_elems, dtype_code(dtype), grad_arena.tensor.data_ptr(), ctypes.addressof(pm),
+            exp_avg_shard.data_ptr(), exp_avg_sq_shard.data_ptr(), float(lr), lr_ptr, beta1, beta2, eps, weight_decay,
+            int(step), None if clip_coef is None else clip_coef.data_ptr(), flags, int(param_arena.use_multicast),
+            self._stream())
+        _lib.check(rc, "ddpb200_sharded_adamw_allgather")
+        param_arena.barrier()
 
 
 _default: Optional[CudaKernels] = None

@@ -20,7 +20,7 @@ class SymmetricArena:
     """A flat buffer that exists at the same offset on every rank of `group`, plus a symmetric
     array of per-chunk partial sums, and the peer map (include/ddp_b200.h: ddpb200_peer_map)."""
 
-    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, group, max_chunks: int):
+    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, group, max_chunks: int = 0):
         import torch.distributed._symmetric_memory as symm_mem
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
@@ -29,9 +29,11 @@ class SymmetricArena:
         self.tensor = symm_mem.empty(max(numel, 1), dtype=dtype, device=device)
         self.tensor.zero_()
         self.hdl = symm_mem.rendezvous(self.tensor, group)
-        self.partials = symm_mem.empty(max(max_chunks, 1), dtype=torch.float32, device=device)
-        self.partials.zero_()
-        self.phdl = symm_mem.rendezvous(self.partials, group)
+        self.partials = self.phdl = None
+        if max_chunks > 0:              # parameter arenas carry no partial sums
+            self.partials = symm_mem.empty(max_chunks, dtype=torch.float32, device=device)
+            self.partials.zero_()
+            self.phdl = symm_mem.rendezvous(self.partials, group)
         self.multicast = int(self.hdl.multicast_ptr or 0)
         mode = os.environ.get("DDPB200_FUSED_MODE", "auto")
         # NVLink bytes per GPU and direction: multicast (1+1/n)S, peer 2(n-1)/n S -> multicast from 4 ranks up
@@ -45,7 +47,7 @@ class SymmetricArena:
             pm = _lib.PeerMap()
             for p in range(self.world):
                 pm.arena[p] = int(self.hdl.buffer_ptrs[p])
-                pm.partials[p] = int(self.phdl.buffer_ptrs[p]) + 4 * chunk_off
+                pm.partials[p] = (int(self.phdl.buffer_ptrs[p]) + 4 * chunk_off) if self.phdl is not None else None
             pm.arena_multicast = self.multicast or None
             pm.rank, pm.world = self.rank, self.world
             self._maps[chunk_off] = pm

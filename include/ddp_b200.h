@@ -199,6 +199,32 @@ DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev_table, int
 DDPB200_API int ddpb200_fold_chunk_partials(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
                                             const float* chunk_partials, float* sumsq_out, void* stream);
 
+/* The reduce-scatter half of the above, for the sharded update: the owner of a chunk
+ * ((absolute chunk id) % world) stores the reduced chunk only in its OWN arena; the per-chunk sums of
+ * squares still go to every rank. Same arguments and barriers as ddpb200_allreduce_sumsq_chunks. */
+DDPB200_API int ddpb200_reduce_scatter_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
+                                                    int64_t chunk_elems, int32_t dtype,
+                                                    const ddpb200_peer_map* peers, int32_t use_multicast,
+                                                    void* stream);
+
+/* ---- §8e/§8f-4  sharded update: AdamW on the owned chunks + all-gather of the parameters -----------
+ * ZeRO-1-style extension of a-6 (no counterpart in the reference; the replicated path above is the
+ * drop-in): after ddpb200_reduce_scatter_sumsq_chunks and the norm finalize, each rank updates only
+ * the chunks it owns — gradients, parameters and its 1/world slice of exp_avg / exp_avg_sq read
+ * from LOCAL memory, arithmetic exactly that of ddpb200_fused_clip_adamw — and stores the new
+ * parameters into every rank's parameter arena (param_peers: symmetric memory with the SAME layout
+ * as the gradient arena; multicast store if use_multicast). dev_table: this rank's device table with
+ * ptr[1] = gradient views inside grad_arena_local. Chunk c's state lives at element offset
+ * (c / world) * chunk_elems of the shards (chunk ids absolute, as in the table). The caller puts a
+ * barrier after this call before any rank reads parameters. Parameters after a step are
+ * bit-identical to the replicated path's. */
+DDPB200_API int ddpb200_sharded_adamw_allgather(
+    const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks, int64_t chunk_elems, int32_t dtype,
+    const void* grad_arena_local, const ddpb200_peer_map* param_peers, void* exp_avg_shard,
+    void* exp_avg_sq_shard, double lr, const float* lr_ptr, double beta1, double beta2, double eps,
+    double weight_decay, int64_t step, const float* clip_coef, uint32_t flags, int32_t use_multicast,
+    void* stream);
+
 /* ---- a-6  fused unscale + clip + AdamW ---------------------------------------
  * Replaces torch.optim.AdamW.step (TORCH/optim/adamw.py:20-49, TORCH/optim/adam.py:
  * 215-272; element math of TORCH/include/ATen/native/cuda/fused_adam_utils.cuh:41-93,

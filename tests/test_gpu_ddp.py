@@ -134,7 +134,45 @@ def _two_rank_worker(rank, ws, port):
             for gabv in (False, True):
                 _train_compare(rank, ws, dtype, gabv, fused=True)
         _fused_vs_nccl(rank, ws, mode)
+        _sharded_vs_replicated(rank, ws, mode)
     dist.destroy_process_group()
+
+
+def _sharded_vs_replicated(rank, ws, mode):
+    """ZeRO-1-style sharded update (reduce-scatter -> norm -> AdamW on owned chunks -> all-gather of
+    parameters) against the replicated path: parameters and norms BIT-IDENTICAL after every step, on
+    every rank, although bucket order and chunk ownership differ between the two."""
+    import ddp_b200
+    mg = _golden_module()
+    dev = torch.device("cuda", rank)
+    for dtype in (torch.bfloat16, torch.float32):
+        torch.manual_seed(0)
+        base = mg.SmallNet().to(dev).to(dtype)
+        a, b = copy.deepcopy(base), copy.deepcopy(base)
+        rep = ddp_b200.DistributedDataParallel(a, device_ids=[rank], bucket_cap_mb=0.008, gradient_as_bucket_view=True,
+                                               fused_allreduce=True)
+        shd = ddp_b200.DistributedDataParallel(b, device_ids=[rank], bucket_cap_mb=0.008, gradient_as_bucket_view=True,
+                                               fused_allreduce=True, shard_optimizer=True)
+        o_rep = ddp_b200.AdamW(a.parameters(), lr=1e-2)
+        o_shd = ddp_b200.ShardedAdamW(shd, lr=1e-2)
+        for s in range(5):
+            ids, tgt = mg.live_batch(40 + s, rank)
+            norms = []
+            for m, o, d in ((rep, o_rep, rep), (shd, o_shd, shd)):
+                loss = torch.nn.functional.cross_entropy(m(ids).flatten(0, 1).float(), tgt.to(dev).flatten())
+                loss.backward()
+                norms.append(d.clip_grad_norm_(0.5, fused_optimizer=o))
+                o.step()
+                o.zero_grad()
+            assert torch.equal(norms[0], norms[1]), (mode, dtype, s)
+            for pa, pb in zip(a.parameters(), b.parameters()):
+                assert torch.equal(pa, pb), (mode, dtype, s)
+        flat = torch.cat([p.detach().reshape(-1) for p in b.parameters()])
+        both = [torch.empty_like(flat) for _ in range(ws)]
+        dist.all_gather(both, flat)
+        assert all(torch.equal(both[0], x) for x in both[1:]), "ranks hold different parameters"
+        sd = o_shd.state_dict()
+        assert sd["sharded"] and sd["step"] == 5 and sd["exp_avg_shard"].abs().sum() > 0
 
 
 def _fused_vs_nccl(rank, ws, mode):

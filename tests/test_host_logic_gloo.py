@@ -216,3 +216,37 @@ def _worker_coalesced_feed(rank, ws, port):
 
 def test_coalesced_gradient_feed(native_lib):
     mp.spawn(_worker_coalesced_feed, args=(2, 29661), nprocs=2, join=True)
+
+
+def _worker_compress_hook(rank, ws, port):
+    """A stock hook that returns a DIFFERENT tensor than the bucket (bf16_compress_hook: cast, divide,
+    allreduce, decompress) goes through the same protocol as in torch: result copied back into the
+    bucket, gradients equal to stock DDP running the same hook."""
+    _setup(rank, ws, port)
+    import copy
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+    mg = _load_golden_module()
+    torch.manual_seed(0)
+    base = mg.SmallNet()
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, bucket_cap_mb=0.008)
+    ours = ddp_b200.DistributedDataParallel(b, bucket_cap_mb=0.008, kernels=OracleKernels())
+    ref.register_comm_hook(None, default_hooks.bf16_compress_hook)
+    ours.register_comm_hook(None, default_hooks.bf16_compress_hook)
+    for s in range(3):
+        for m in (ref, ours):
+            m.zero_grad()
+            ids, tgt = mg.live_batch(30 + s, rank)
+            torch.nn.functional.cross_entropy(m(ids).flatten(0, 1), tgt.flatten()).backward()
+        for pr, po in zip(a.parameters(), b.parameters()):
+            assert torch.equal(pr.grad, po.grad), s
+        n_ref = torch.nn.utils.clip_grad_norm_(a.parameters(), 1e9)
+        n_our = ours.clip_grad_norm_(1e9)
+        assert abs(float(n_ref) - float(n_our)) <= 1e-6 * float(n_ref)
+    dist.destroy_process_group()
+
+
+def test_compress_comm_hook(native_lib):
+    mp.spawn(_worker_compress_hook, args=(2, 29671), nprocs=2, join=True)
