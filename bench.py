@@ -229,7 +229,6 @@ def run_ours(args):
     order = grad_ready_order(len(params), cfg["layers"], cfg["tie"])
 
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
-    norm_host = torch.empty(2, dtype=torch.float32).pin_memory()
 
     def step(i=None, first=False):
         ddp.reduce_gradients(grads, order=order if first else None)

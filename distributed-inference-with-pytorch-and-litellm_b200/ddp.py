@@ -24,7 +24,6 @@ modules and ``join()`` are outside the path this package covers and raise.
 from __future__ import annotations
 
 import os
-import sys
 import weakref
 from contextlib import contextmanager
 from typing import Callable, List, Optional

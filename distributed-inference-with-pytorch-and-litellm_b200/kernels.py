@@ -9,7 +9,7 @@ world_size-2 gloo tests drive the scheduler on CPU with a checker backend define
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional, Sequence
+from typing import Optional, Sequence
 
 import numpy as np
 import torch

@@ -6,9 +6,7 @@ the switch supports it, a multicast alias) into this process; it also provides t
 The bytes are moved by csrc/fused_allreduce.cu."""
 from __future__ import annotations
 
-import ctypes
 import os
-from typing import Optional
 
 import torch
 import torch.distributed as dist

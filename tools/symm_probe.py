@@ -1,5 +1,5 @@
 """Probe: does torch's symmetric memory (peer-mapped + NVLS multicast) come up on this box?"""
-import os, sys, time
+import os, time
 import torch, torch.distributed as dist
 import torch.distributed._symmetric_memory as symm_mem
 
