@@ -215,6 +215,13 @@ def run_ours(args):
         print(fused_note, file=sys.stderr, flush=True)
         ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
                                                fused_allreduce=False)
+    if ws > 1 and args.allreduce == "fused" and not zero1:
+        ok = torch.tensor([1 if ddp._fused else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok) == 0 and ddp._fused:         # another rank fell back: all ranks must issue the same collectives
+            fused_note = "fused allreduce unavailable on another rank; NCCL used"
+            ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
+                                                   fused_allreduce=False)
     if zero1:
         opt = ddp_b200.ShardedAdamW(ddp, lr=LR, weight_decay=1e-2)
     else:
@@ -346,6 +353,7 @@ def run_ours(args):
             "metric": METRIC, "value": ws * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ws,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "arithmetic": "fp32 opmath on bf16 storage (p, g, exp_avg, exp_avg_sq), as torch's fused AdamW",
             "data": "synthetic", "impl": "ours" + ("-zero1" if zero1 else ""),
             "config": {"workload": f"{args.workload}-arch parameter set, bf16 p/g/m/v, {len(params)} tensors, "
                                    f"{total} elements; gradient_as_bucket_view, 25 MiB buckets "
