@@ -278,65 +278,72 @@ def run_ours(args):
     launches += 2 * (stats1.get("fused_allreduces", 0) - stats0.get("fused_allreduces", 0))   # allreduce kernel + fold
     allreduces = stats1["allreduces"] - stats0["allreduces"]
 
-    # ---- timed: end to end from HOST gradients ---------------------------------------------------
-    # Each step's gradients arrive from pinned host memory (H2D inside the timed region) and the
-    # pre-clip total norm is read back on the host (D2H). The copies run bucket by bucket on a copy
-    # stream into one of two landing buffers, so a bucket is processed as soon as it has landed and
-    # the update of step k overlaps the transfer of step k+1.
-    e2e_steps = max(2, min(args.steps, 10))
-    layout = ddp.bucket_layout()
-    order_now = [pi for b in layout for pi in b["parameters"]]
-    host_g = torch.empty(total, dtype=dtype).pin_memory()
-    host_g.copy_(gflat)
-    land = [gflat, torch.empty_like(gflat)]
-    land_views, bucket_span = [], []
-    for buf in land:                         # landing buffers are laid out in bucket order
-        views, o = [None] * len(params), 0
-        for pi in order_now:
-            views[pi] = buf[o:o + numel[pi]].view(shapes[pi])
-            o += numel[pi]
-        land_views.append(views)
-    o = 0
-    for b in layout:
-        bucket_span.append((o, o + b["numel"]))
-        o += b["numel"]
-    copy_stream = torch.cuda.Stream(device=dev)
-    landed = [[torch.cuda.Event() for _ in layout] for _ in land]
-    consumed = [torch.cuda.Event() for _ in land]
-    norm_ready = [torch.cuda.Event() for _ in land]
-    norm_host2 = [torch.empty(2, dtype=torch.float32).pin_memory() for _ in land]
-    for ev_ in consumed:
-        ev_.record()
+    def run_e2e(e2e_steps):
+        # ---- timed: end to end from HOST gradients ---------------------------------------------------
+        # Each step's gradients arrive from pinned host memory (H2D inside the timed region) and the
+        # pre-clip total norm is read back on the host (D2H). The copies run bucket by bucket on a copy
+        # stream into one of two landing buffers, so a bucket is processed as soon as it has landed and
+        # the update of step k overlaps the transfer of step k+1.
+        layout = ddp.bucket_layout()
+        order_now = [pi for b in layout for pi in b["parameters"]]
+        host_g = torch.empty(total, dtype=dtype).pin_memory()
+        host_g.copy_(gflat)
+        land = [gflat, torch.empty_like(gflat)]
+        land_views, bucket_span = [], []
+        for buf in land:                         # landing buffers are laid out in bucket order
+            views, o = [None] * len(params), 0
+            for pi in order_now:
+                views[pi] = buf[o:o + numel[pi]].view(shapes[pi])
+                o += numel[pi]
+            land_views.append(views)
+        o = 0
+        for b in layout:
+            bucket_span.append((o, o + b["numel"]))
+            o += b["numel"]
+        copy_stream = torch.cuda.Stream(device=dev)
+        landed = [[torch.cuda.Event() for _ in layout] for _ in land]
+        consumed = [torch.cuda.Event() for _ in land]
+        norm_ready = [torch.cuda.Event() for _ in land]
+        norm_host2 = [torch.empty(2, dtype=torch.float32).pin_memory() for _ in land]
+        for ev_ in consumed:
+            ev_.record()
 
-    def h2d(slot):
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(consumed[slot])             # the buffer's previous reader is done
-            for b, (lo, hi) in enumerate(bucket_span):
-                land[slot][lo:hi].copy_(host_g[lo:hi], non_blocking=True)
-                landed[slot][b].record()
+        def h2d(slot):
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[slot])             # the buffer's previous reader is done
+                for b, (lo, hi) in enumerate(bucket_span):
+                    land[slot][lo:hi].copy_(host_g[lo:hi], non_blocking=True)
+                    landed[slot][b].record()
 
-    sync_all()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    last_norm = 0.0
-    h2d(0)
-    for it in range(e2e_steps):
-        slot = it % 2
-        if it + 1 < e2e_steps:
-            h2d(1 - slot)                                      # next step's gradients start moving now
-        cur = torch.cuda.current_stream()
-        ddp.reduce_gradients(land_views[slot], before_bucket=lambda b, _idx: cur.wait_event(landed[slot][b]))
-        ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
-        norm_host2[slot].copy_(ddp._norm_out, non_blocking=True)
-        norm_ready[slot].record()
-        opt.step()
-        consumed[slot].record()
-        opt.zero_grad()
-        norm_ready[slot].synchronize()                         # the step's result, on the host
-        last_norm = float(norm_host2[slot][0])
-    e1.record()
-    sync_all()
-    e2e_ms = e0.elapsed_time(e1)
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last_norm = 0.0
+        h2d(0)
+        for it in range(e2e_steps):
+            slot = it % 2
+            if it + 1 < e2e_steps:
+                h2d(1 - slot)                                      # next step's gradients start moving now
+            cur = torch.cuda.current_stream()
+            ddp.reduce_gradients(land_views[slot], before_bucket=lambda b, _idx: cur.wait_event(landed[slot][b]))
+            ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
+            norm_host2[slot].copy_(ddp._norm_out, non_blocking=True)
+            norm_ready[slot].record()
+            opt.step()
+            consumed[slot].record()
+            opt.zero_grad()
+            norm_ready[slot].synchronize()                         # the step's result, on the host
+            last_norm = float(norm_host2[slot][0])
+        e1.record()
+        sync_all()
+        e2e_ms = e0.elapsed_time(e1)
+        return e2e_ms, last_norm
+
+    e2e_steps = 0 if args.skip_e2e else max(2, min(args.steps, 10))
+    if e2e_steps:
+        e2e_ms, last_norm = run_e2e(e2e_steps)
+    else:
+        e2e_ms, last_norm = float("nan"), float(ddp._norm_out[0])
 
     t = torch.tensor([ms, e2e_ms, adamw_ms], dtype=torch.float64, device=dev)
     if ws > 1:
@@ -359,10 +366,10 @@ def run_ours(args):
                                    f"{total} elements; gradient_as_bucket_view, 25 MiB buckets "
                                    f"({len(bucket_bytes)} after rebuild), max_norm {MAX_NORM}, AdamW lr {LR}",
                        "global_batch": f"{ws} replicas x 1 synthetic gradient set",
-                       "l2": "working set per step 12.4 GB >> 126 MB L2; no flush needed",
+                       "l2": f"working set per step {16 * total / 1e9:.1f} GB >> 126 MB L2; no flush needed",
                        "parallelism": f"dp{ws}" + (" + sharded optimizer (ZeRO-1 style)" if zero1 else "")},
             "steps_per_s": args.steps / (ms * 1e-3),
-            "e2e": {"value": ws * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "steps": e2e_steps,
+            "e2e": {"value": (ws * e2e_steps / (e2e_ms * 1e-3)) if e2e_steps else None, "unit": UNIT, "steps": e2e_steps,
                     "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8,
                     "note": "gradients of each step copied from pinned host memory (bucket by bucket, double "
                             "buffered); total norm read back on the host every step"},
@@ -514,6 +521,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=list(WORKLOADS), default="llama-3.2-1b")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true", help="skip the host-gradient leg (large workloads: pinned host memory)")
     ap.add_argument("--zero1", action="store_true",
                     help="N>1: the sharded update (reduce-scatter + AdamW on owned chunks + all-gather of parameters) "
                          "instead of the drop-in replicated path; an extension, not the default")
