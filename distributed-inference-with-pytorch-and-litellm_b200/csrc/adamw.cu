@@ -54,7 +54,8 @@ __device__ __forceinline__ bool all_aligned(const void* P, const void* Gp, const
          group_aligned<SDT, G>(V);
 }
 
-template <class Tab, int PDT, int GDT, int SDT, int MODE, int CT>
+// MAXVEC: widest access the kernel may use (32 = 256-bit, 16 = 128-bit: fewer live registers)
+template <class Tab, int PDT, int GDT, int SDT, int MODE, int CT, int MAXVEC = 32>
 __global__ void __launch_bounds__(kThreads, CT)
 adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
              AdamScalars a, const float* __restrict__ lr_ptr, const float* __restrict__ clip_ptr,
@@ -77,7 +78,7 @@ adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chun
     char* V = static_cast<char*>(tab.ptr(s, 3)) + start * ElemOf<SDT>::size;
 
     int64_t done = 0;
-    if (all_aligned<PDT, GDT, SDT, GroupSize<32, any_f32>::G>(P, Gp, M, V))
+    if (MAXVEC >= 32 && all_aligned<PDT, GDT, SDT, GroupSize<32, any_f32>::G>(P, Gp, M, V))
       done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 32>(P, Gp, M, V, len, a, r, store_g);
     else if (all_aligned<PDT, GDT, SDT, GroupSize<16, any_f32>::G>(P, Gp, M, V))
       done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 16>(P, Gp, M, V, len, a, r, store_g);
@@ -104,15 +105,31 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
       int err = 0;
       const int sms = sm_count_cached(&err);
       if (err) return err;
-      // CTAs per SM, measured on B200 at Llama-1B size (tools/kbench.py, profiles/r01_kbench.txt):
-      // all-bf16 fast modes peak at 3 (6.3 TB/s; 2 -> 5.6, 4 -> 5.0 with spills); anything with an
-      // fp32 stream, and the general mode, peak at 2 (6.6 TB/s fp32).
+      // CTAs per SM and access width, measured on B200 at Llama-1B size (tools/kbench.py,
+      // profiles/r01_kbench_ctas.txt), burst (10 launches) / sustained (600 launches, power cap active):
+      //   all-bf16 fast modes: 256-bit x 3 CTAs/SM 6.28 / 5.94 TB/s; 128-bit x 4 CTAs/SM 6.22 / 6.20 TB/s
+      //                        (128-bit x 3: 5.54, x 5: 5.54 with spills; 256-bit x 4: 5.05 with spills)
+      //   -> 128-bit x 4: the narrower groups need fewer live registers, the fourth CTA hides latency
+      //      when the power cap pulls the SM clock down, which is the state a training run lives in.
+      //   anything with an fp32 stream, and the general mode: 256-bit x 2 CTAs/SM (6.6 TB/s fp32).
       constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
-      constexpr int CT = (!any_f32 && MODE != kModeGeneral) ? 3 : 2;
+      constexpr bool narrow = !any_f32 && MODE != kModeGeneral;
+      constexpr int CT = narrow ? 4 : 2;
+      constexpr int MAXVEC = narrow ? 16 : 32;
       const int64_t cap = (int64_t)sms * CT;
       const int grid = (int)(chunks < cap ? chunks : cap);
       if (grid == 0) return 0;
-      adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT><<<grid, kThreads, 0, st>>>(
+      // A/B switch for tools/kbench.py only: DDPB200_ADAMW_WIDE=1 selects 256-bit x 3 CTAs/SM
+      static const bool wide = [] { const char* e = getenv("DDPB200_ADAMW_WIDE"); return e && atoi(e) == 1; }();
+      if constexpr (narrow) {
+        if (wide) {
+          const int64_t wcap = (int64_t)sms * 3;
+          adamw_kernel<Tab, PDT, GDT, SDT, MODE, 3, 32><<<(int)(chunks < wcap ? chunks : wcap), kThreads, 0, st>>>(
+              tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
+          return (int)cudaGetLastError();
+        }
+      }
+      adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT, MAXVEC><<<grid, kThreads, 0, st>>>(
           tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
       return (int)cudaGetLastError();
     });

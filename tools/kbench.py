@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--reps", type=int, default=10)
     ap.add_argument("--segments", default="llama")
     ap.add_argument("--only", default="")
+    ap.add_argument("--sustained", type=int, default=0)
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     K = ddp_b200.CudaKernels()
@@ -89,6 +90,17 @@ def main():
             K.adamw(tab, dt, dt, dt, step=step[0], clip_coef=coef, round_clipped=False, **hp)
 
         report(f"adamw {tag} clip (fast)", timeit(adam_clip, args.reps), 7 * es * n)
+        if args.sustained:
+            # long back-to-back run: the power cap pulls SM clocks down, which this kernel follows
+            import subprocess
+            smi = subprocess.Popen(["nvidia-smi", "--query-gpu=clocks.sm,power.draw", "--format=csv,noheader,nounits", "-lms", "50"],
+                                   stdout=subprocess.PIPE, text=True)
+            report(f"adamw {tag} clip (fast), {args.sustained} launches back to back", timeit(adam_clip, args.sustained), 7 * es * n)
+            smi.terminate()
+            samples = [l.split(",") for l in smi.stdout.read().strip().splitlines() if "," in l]
+            clk = sorted(float(x[0]) for x in samples)
+            print(f"    sm clock median {clk[len(clk)//2]:.0f} MHz over {len(clk)} samples, power max {max(float(x[1]) for x in samples):.0f} W", flush=True)
+            continue
         report(f"adamw {tag} no clip (fast)", timeit(adam_plain, args.reps), 7 * es * n)
         report(f"adamw {tag} general mode", timeit(adam_general, args.reps), 7 * es * n)
         # torch's fused AdamW on the same box (list of the same tensors)
