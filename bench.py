@@ -180,6 +180,31 @@ def adamw_traffic_from_profile():
         return None
 
 
+def bind_to_gpu_numa_node(dev_index):
+    """Run this rank on the CPUs NVML lists as local to its GPU, so that the pinned host buffers of the
+    end-to-end leg are first-touched on the GPU's NUMA node (8 ranks otherwise share one node's memory
+    and root complex). Returns the number of CPUs bound to, or None if NVML is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(dev_index).uuid)
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(dev_index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [w * 64 + b for w, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 # ---- our arm ------------------------------------------------------------------------------------
 def run_ours(args):
     import ddp_b200
@@ -190,6 +215,8 @@ def run_ours(args):
     assert ws == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={ws} (launch N>1 with torchrun)"
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    all_cpus = os.sched_getaffinity(0)
+    numa_cpus = bind_to_gpu_numa_node(local) if not args.no_numa_bind else None
     if "MASTER_ADDR" not in os.environ:
         os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(free_port())
     dist.init_process_group("nccl", rank=rank, world_size=ws, device_id=dev)
@@ -370,7 +397,7 @@ def run_ours(args):
                        "parallelism": f"dp{ws}" + (" + sharded optimizer (ZeRO-1 style)" if zero1 else "")},
             "steps_per_s": args.steps / (ms * 1e-3),
             "e2e": {"value": (ws * e2e_steps / (e2e_ms * 1e-3)) if e2e_steps else None, "unit": UNIT, "steps": e2e_steps,
-                    "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8,
+                    "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8, "numa_local_cpus": numa_cpus,
                     "note": "gradients of each step copied from pinned host memory (bucket by bucket, double "
                             "buffered); total norm read back on the host every step"},
             "gpu_launches": launches,
@@ -393,6 +420,7 @@ def run_ours(args):
         measure_allreduce(ddp, ws, dev)
 
     if rank == 0 and ws == 1 and not args.no_cpu_baseline:
+        os.sched_setaffinity(0, all_cpus)            # the CPU baseline gets every host core
         out["cpu_baseline"] = cpu_baseline_sample(cfg, total)
     if rank == 0:
         print(json.dumps(out))
@@ -521,6 +549,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=list(WORKLOADS), default="llama-3.2-1b")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to its GPU's NUMA-local CPUs")
     ap.add_argument("--skip-e2e", action="store_true", help="skip the host-gradient leg (large workloads: pinned host memory)")
     ap.add_argument("--zero1", action="store_true",
                     help="N>1: the sharded update (reduce-scatter + AdamW on owned chunks + all-gather of parameters) "
