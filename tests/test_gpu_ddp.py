@@ -230,3 +230,54 @@ def test_launch_script_single_gpu():
                          capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stderr[-3000:]
     assert "done: 5 steps" in res.stderr and "Using device: cuda:0" in res.stderr
+
+
+class _MixedNet(torch.nn.Module):
+    """bf16 matrices with fp32 norm parameters and an EMPTY parameter: two bucket dtypes, two optimizer
+    launches, a zero-length segment."""
+
+    def __init__(self):
+        super().__init__()
+        self.fc1 = torch.nn.Linear(32, 64).to(torch.bfloat16)
+        self.ln = torch.nn.LayerNorm(64)                      # fp32
+        self.fc2 = torch.nn.Linear(64, 16).to(torch.bfloat16)
+        self.empty = torch.nn.Parameter(torch.zeros(0))
+
+    def forward(self, x):
+        h = torch.relu(self.fc1(x.to(torch.bfloat16)))
+        h = self.ln(h.float()).to(torch.bfloat16)
+        return self.fc2(h).float().sum() + self.empty.sum()
+
+
+@pytest.mark.parametrize("gabv", [False, True])
+def test_mixed_dtype_and_empty_parameters(pg1, gabv):
+    import ddp_b200
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(3)
+    base = _MixedNet().to(dev)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, device_ids=[0], bucket_cap_mb=0.004, gradient_as_bucket_view=gabv)
+    ours = ddp_b200.DistributedDataParallel(b, device_ids=[0], bucket_cap_mb=0.004, gradient_as_bucket_view=gabv)
+    o_ref = torch.optim.AdamW(a.parameters(), lr=1e-2, fused=True)
+    o_our = ddp_b200.AdamW(b.parameters(), lr=1e-2)
+    for s in range(4):
+        x = torch.randn(8, 32, device=dev, generator=torch.Generator(device=dev).manual_seed(s))
+        ref(x).backward()
+        ours(x).backward()
+        n_ref = torch.nn.utils.clip_grad_norm_(a.parameters(), 0.1)
+        n_our = ours.clip_grad_norm_(0.1, fused_optimizer=o_our)
+        assert abs(float(n_ref) - float(n_our)) <= 2e-3 * float(n_ref) * (1 + s)
+        o_ref.step(); o_our.step()
+        o_ref.zero_grad(); o_our.zero_grad()
+    assert o_our.launches_last_step == 2                       # one per dtype group
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        if pa.numel():
+            tol = dict(rtol=0, atol=2e-2) if pa.dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-5)
+            assert torch.allclose(pa.float(), pb.float(), **tol), (pa.dtype, float((pa.float() - pb.float()).abs().max()))
+    # free function on a mixed list: norm in fp32 (not all grads are bf16), grads scaled in place
+    x = torch.randn(8, 32, device=dev)
+    ref(x).backward(); ours(x).backward()
+    n_ref = torch.nn.utils.clip_grad_norm_(a.parameters(), 0.05)
+    n_our = ddp_b200.clip_grad_norm_(b.parameters(), 0.05)
+    assert n_our.dtype == n_ref.dtype
+    assert abs(float(n_ref) - float(n_our)) <= 1e-2 * float(n_ref)
