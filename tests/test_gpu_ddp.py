@@ -135,7 +135,41 @@ def _two_rank_worker(rank, ws, port):
                 _train_compare(rank, ws, dtype, gabv, fused=True)
         _fused_vs_nccl(rank, ws, mode)
         _sharded_vs_replicated(rank, ws, mode)
+    os.environ["DDPB200_FUSED_MODE"] = "auto"
+    for fused in (False, True):
+        _mixed_dtype_two_ranks(rank, fused)
     dist.destroy_process_group()
+
+
+def _mixed_dtype_two_ranks(rank, fused):
+    """bf16 + fp32 parameters (two bucket dtypes, two arenas) across two ranks, NCCL and fused."""
+    import ddp_b200
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(3)
+    base = _MixedNet().to(dev)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, device_ids=[rank], bucket_cap_mb=0.004)
+    ours = ddp_b200.DistributedDataParallel(b, device_ids=[rank], bucket_cap_mb=0.004, gradient_as_bucket_view=True,
+                                            fused_allreduce=fused)
+    o_ref = torch.optim.AdamW(a.parameters(), lr=1e-2, fused=True)
+    o_our = ddp_b200.AdamW(b.parameters(), lr=1e-2)
+    for s in range(4):
+        x = torch.randn(8, 32, device=dev, generator=torch.Generator(device=dev).manual_seed(10 * s + rank))
+        ref(x).backward()
+        ours(x).backward()
+        for pa, pb in zip(a.parameters(), b.parameters()):
+            if pa.numel() and s == 0:
+                tol = dict(rtol=2 ** -6, atol=1e-3) if pa.dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-6)
+                assert torch.allclose(pa.grad.float(), pb.grad.float(), **tol), (fused, pa.dtype)
+        n_ref = torch.nn.utils.clip_grad_norm_(a.parameters(), 0.1)
+        n_our = ours.clip_grad_norm_(0.1, fused_optimizer=o_our)
+        assert abs(float(n_ref) - float(n_our)) <= 3e-3 * float(n_ref) * (1 + s), (fused, s, float(n_ref), float(n_our))
+        o_ref.step(); o_our.step()
+        o_ref.zero_grad(); o_our.zero_grad()
+    flat = torch.cat([p.detach().float().reshape(-1) for p in b.parameters()])
+    both = [torch.empty_like(flat) for _ in range(2)]
+    dist.all_gather(both, flat)
+    assert torch.equal(both[0], both[1]), "ranks diverged"
 
 
 def _sharded_vs_replicated(rank, ws, mode):
