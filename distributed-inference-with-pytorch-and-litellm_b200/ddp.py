@@ -140,6 +140,8 @@ class DistributedDataParallel(nn.Module):
             self._sync_module_states()
 
         self._comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self._cuda else None
+        self._use_side_stream = os.environ.get("PYTORCH_DDP_USE_SIDE_STREAM", "1") == "1"
+        self._copy_stream = None
         # bucket allreduce + norm as ONE kernel over NVLink peer memory instead of NCCL + a norm pass
         if fused_allreduce is None:
             fused_allreduce = os.environ.get("DDPB200_FUSED_ALLREDUCE", "0") == "1"
@@ -336,8 +338,22 @@ class DistributedDataParallel(nn.Module):
         return self.module(*inputs, **kwargs)
 
     def _to_device(self, obj):
+        """Inputs to the module's device, as torch's DDP does when device_ids is given: host tensors are
+        copied on a side stream (PYTORCH_DDP_USE_SIDE_STREAM, distributed.py:855-858) so that a pinned
+        batch streams in behind the previous step's tail; the compute stream waits for the copy."""
         if isinstance(obj, torch.Tensor):
-            return obj if obj.device == self.device else obj.to(self.device, non_blocking=True)
+            if obj.device == self.device:
+                return obj
+            if self._cuda and self._use_side_stream and obj.device.type == "cpu":
+                if self._copy_stream is None:
+                    self._copy_stream = torch.cuda.Stream(device=self.device)
+                with torch.cuda.stream(self._copy_stream):
+                    out = obj.to(self.device, non_blocking=True)
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_stream(self._copy_stream)
+                out.record_stream(cur)
+                return out
+            return obj.to(self.device, non_blocking=True)
         if isinstance(obj, tuple):
             return tuple(self._to_device(o) for o in obj)
         if isinstance(obj, list):

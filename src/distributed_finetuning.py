@@ -109,7 +109,7 @@ def main():
         texts, labels = synthetic_imdb()
         data = CustomDataset(texts, labels)
         sampler = DistributedSampler(data, num_replicas=world_size, rank=rank)
-        loader = DataLoader(data, batch_size=4, sampler=sampler)
+        loader = DataLoader(data, batch_size=4, sampler=sampler, pin_memory=torch.cuda.is_available())
 
         model = build_model(CONFIG["TRAIN_MODEL"], device, torch.bfloat16 if on_gpu else torch.float32)
         if on_gpu:
