@@ -78,6 +78,39 @@ class ShardedAdamW:
                 "chunk_elems": self.ddp._view_table.chunk_elems, "exp_avg_shard": self.exp_avg,
                 "exp_avg_sq_shard": self.exp_avg_sq, "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
 
+    def consolidated_state_dict(self) -> dict:
+        """COLLECTIVE: gather every rank's shards and return the state in ``torch.optim.AdamW``'s
+        format (per parameter ``step`` / ``exp_avg`` / ``exp_avg_sq``, in DDP registration order), so a
+        sharded run can be checkpointed into, or compared with, the replicated optimizer. Chunk a
+        of the table lives on rank a % world at slot a // world."""
+        import torch.distributed as dist
+        ddp = self.ddp
+        ws, tab = ddp.world_size, ddp._view_table
+        ce = tab.chunk_elems
+        gathered = {}
+        for name, shard in (("exp_avg", self.exp_avg), ("exp_avg_sq", self.exp_avg_sq)):
+            parts = [torch.empty_like(shard) for _ in range(ws)]
+            dist.all_gather(parts, shard, group=ddp.process_group)
+            gathered[name] = parts
+        state = {}
+        for row, pi in enumerate(ddp._order):
+            p = ddp._params[pi]
+            n = p.numel()
+            first_chunk = int(tab.chunk_begins[row])
+            ent = {"step": torch.tensor(float(self.step_count))}
+            for name in ("exp_avg", "exp_avg_sq"):
+                out = torch.empty(n, dtype=self.exp_avg.dtype, device=p.device)
+                for k in range(int(tab.chunk_begins[row + 1]) - first_chunk):
+                    a = first_chunk + k
+                    ln = min(ce, n - k * ce)
+                    out[k * ce:k * ce + ln] = gathered[name][a % ws][(a // ws) * ce:(a // ws) * ce + ln]
+                ent[name] = out.view_as(p)
+            state[pi] = ent
+        g = {k: v for k, v in self.param_groups[0].items() if k != "params"}
+        g.update(amsgrad=False, foreach=None, capturable=False, differentiable=False, fused=None,
+                 decoupled_weight_decay=True, params=list(range(len(ddp._params))))
+        return {"state": {i: state[i] for i in sorted(state)}, "param_groups": [g]}
+
     def load_state_dict(self, sd: dict) -> None:
         if not sd.get("sharded") or sd["world_size"] != self.ddp.world_size or sd["rank"] != self.ddp.rank:
             raise ValueError("ShardedAdamW.load_state_dict: shard of another rank / world size")

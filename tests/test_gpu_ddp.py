@@ -207,6 +207,16 @@ def _sharded_vs_replicated(rank, ws, mode):
         assert all(torch.equal(both[0], x) for x in both[1:]), "ranks hold different parameters"
         sd = o_shd.state_dict()
         assert sd["sharded"] and sd["step"] == 5 and sd["exp_avg_shard"].abs().sum() > 0
+        # the shards, gathered into torch's per-parameter format, equal the replicated optimizer's
+        # state bit for bit, and load into a stock torch.optim.AdamW
+        full = o_shd.consolidated_state_dict()
+        rep_state = o_rep.state_dict()["state"]
+        assert set(full["state"]) == set(rep_state)
+        for i, st in full["state"].items():
+            assert float(st["step"]) == float(rep_state[i]["step"]) == 5.0
+            assert torch.equal(st["exp_avg"], rep_state[i]["exp_avg"]), (mode, dtype, i)
+            assert torch.equal(st["exp_avg_sq"], rep_state[i]["exp_avg_sq"]), (mode, dtype, i)
+        torch.optim.AdamW(list(b.parameters()), lr=1e-2).load_state_dict(full)
 
 
 def _fused_vs_nccl(rank, ws, mode):
