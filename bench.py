@@ -475,9 +475,11 @@ def stock_cpu_step_rate(cfg, steps, warmup, layers_sample=None):
     total = sum(p.numel() for p in params)
     own = not dist.is_initialized()
     if own:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["MASTER_PORT"] = str(free_port())
-        dist.init_process_group("gloo", rank=0, world_size=1)
+        # a file store of its own: under torchrun both env:// and tcp:// would try to join the elastic
+        # agent's store (TORCHELASTIC_USE_AGENT_STORE) instead of creating one for this 1-rank group
+        import tempfile
+        store_file = os.path.join(tempfile.mkdtemp(prefix="ddpb200_ref_"), "store")
+        dist.init_process_group("gloo", init_method=f"file://{store_file}", rank=0, world_size=1)
         pg = None
     else:
         pg = dist.new_group(ranks=[dist.get_rank()], backend="gloo")
@@ -521,6 +523,8 @@ def run_reference(args):
     if rank != 0:
         return
     cfg = WORKLOADS[args.workload]
+    # every host core: torchrun exports OMP_NUM_THREADS=1 to its workers, which is not the reference's best
+    torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
     total_full = sum(int(torch.Size(s).numel()) for s in llama_param_shapes(**cfg))
     # bounded: the whole run must end within minutes on host cores -> 4-layer slice, scaled by elements
     layers = 4 if cfg["layers"] > 4 else None
