@@ -60,10 +60,11 @@ extern "C" {
                                   lifetime to manage) — for pointers that change every step    */
 #define DDPB200_TABLE_DEVICE 1 /* device memory: built once, reused every step                  */
 
-/* One segment (parameter tensor) of a multi-tensor launch. 48 bytes, device-resident
- * table built once by the host and reused every step. What ptr[0..3] mean is stated
- * per entry point. chunk_begin is the exclusive prefix sum of ceil(numel/chunk_elems). */
-/* A table may be sliced: pass table+first, the slice's n and chunk count; kernels rebase on
+/* One segment (parameter tensor) of a multi-tensor launch, 48 bytes. A table of segments lives
+ * on the device (built once, reused every step) or on the host (see DDPB200_TABLE_*). What
+ * ptr[0..3] mean is stated per entry point. chunk_begin is the exclusive prefix sum of
+ * ceil(numel/chunk_elems) over the table (ddpb200_plan_chunks fills it).
+ * A table may be sliced: pass table+first, the slice's n and chunk count; kernels rebase on
  * the first chunk_begin they see. */
 typedef struct ddpb200_seg {
   void*   ptr[4];
