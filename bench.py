@@ -453,10 +453,28 @@ def measure_allreduce(ddp, ws, dev):
     Sa = sum(a.numel() * a.element_size() for a in arenas)
     ms_one = timed(lambda: [dist.all_reduce(a) for a in arenas])
     ms_per = timed(lambda: [dist.all_reduce(b) for b in bufs])
+    fused = None
+    if ddp._fused:
+        # the path's own collective: allreduce AND per-tensor sums of squares in one kernel (+2 barriers + fold)
+        import ddp_b200
+        k = ddp._kernels
+        ss = torch.empty_like(ddp._sumsq)
+        tab = ddp._view_table
+
+        def run_fused():
+            for bk_dt, arena in ddp._sym.items():
+                rows = [bk for bk in ddp._buckets if bk.dtype == bk_dt]
+                first, n = rows[0].first, sum(bk.n for bk in rows)
+                k.allreduce_sumsq(tab, bk_dt, arena, ss[first:first + n], first=first, count=n, scatter=False)
+        if len(ddp._sym) == 1:
+            ms_f = timed(run_fused)
+            fused = {"ms": ms_f, "busbw_equiv_gbs": Sa / (ms_f * 1e-3) * 2 * (ws - 1) / ws / 1e9,
+                     "mode": "multicast" if any(a.use_multicast for a in ddp._sym.values()) else "peer",
+                     "includes": "allreduce + per-tensor sum of squares + 2 barriers + fold"}
     for a in arenas:
         a.zero_()
     f = 2 * (ws - 1) / ws / 1e9
-    return {"bytes_per_step": S, "buckets": len(bufs),
+    return {"bytes_per_step": S, "buckets": len(bufs), "fused_kernel": fused,
             "coalesced": {"ms": ms_one, "busbw_gbs": Sa / (ms_one * 1e-3) * f, "frac_of_900": Sa / (ms_one * 1e-3) * f / 900.0},
             "per_bucket": {"ms": ms_per, "busbw_gbs": S / (ms_per * 1e-3) * f, "frac_of_900": S / (ms_per * 1e-3) * f / 900.0}}
 
