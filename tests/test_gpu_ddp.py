@@ -327,3 +327,34 @@ def test_mixed_dtype_and_empty_parameters(pg1, gabv):
     n_our = ddp_b200.clip_grad_norm_(b.parameters(), 0.05)
     assert n_our.dtype == n_ref.dtype
     assert abs(float(n_ref) - float(n_our)) <= 1e-2 * float(n_ref)
+
+
+def test_grad_scaler_unscale_path(pg1):
+    """torch.amp.GradScaler hands grad_scale / found_inf to optimizers that declare
+    _step_supports_amp_scaling; the fused kernel then unscales inside the update (the "unscale" of the
+    north star). Same flow on torch.optim.AdamW(fused=True): parameters agree, a step with an inf
+    gradient is skipped by both, and the scaler backs off."""
+    import ddp_b200
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(5)
+    base = torch.nn.Sequential(torch.nn.Linear(40, 64), torch.nn.Tanh(), torch.nn.Linear(64, 8)).to(dev)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    o_ref = torch.optim.AdamW(a.parameters(), lr=1e-2, fused=True)
+    o_our = ddp_b200.AdamW(b.parameters(), lr=1e-2)
+    s_ref = torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=1000)
+    s_our = torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=1000)
+    for s in range(5):
+        x = torch.randn(16, 40, device=dev, generator=torch.Generator(device=dev).manual_seed(s))
+        for m, o, sc in ((a, o_ref, s_ref), (b, o_our, s_our)):
+            loss = m(x).pow(2).mean()
+            sc.scale(loss).backward()
+            if s == 3:                                   # poison one gradient: the step must be skipped
+                next(m.parameters()).grad[0, 0] = float("inf")
+            sc.step(o)
+            sc.update()
+            o.zero_grad()
+        assert float(s_ref.get_scale()) == float(s_our.get_scale())
+        for pa, pb in zip(a.parameters(), b.parameters()):
+            assert torch.allclose(pa, pb, rtol=1e-5, atol=1e-6), (s, float((pa - pb).abs().max()))
+    assert float(s_our.get_scale()) == 512.0             # backed off once
+    assert float(o_our.state[next(b.parameters())]["step"]) == 4.0   # 5 calls, one skipped
