@@ -328,6 +328,8 @@ class DistributedDataParallel(nn.Module):
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self._rebuild_buckets()
             self._prepare_for_backward()
+        elif torch.is_grad_enabled():
+            self._sumsq_valid = False        # no_sync(): gradients will change without being reduced or normed
         if self.broadcast_buffers and self.world_size > 1 and self.require_backward_grad_sync:
             bufs = [b for _, b in self.module.named_buffers()]
             if bufs:
