@@ -41,6 +41,13 @@ def test_bucket_tables_of_survey(layouts):
     # the survey's tables use the live grad-ready order; reversed registration order (used by the
     # fixture) gives the same counts for GPT-2 and differs by the position of the norm weights only
     assert got["gpt2-small-fp32"] == want["gpt2-small-fp32"]
+    # byte sizes of the GPT-2 buckets = what a live stock DDP run logged as rebuilt_bucket_sizes
+    # ("9446400, 28351488 x 11, 176446464")
+    c = [x for x in layouts if x["name"] == "gpt2-small-fp32/rebuild-1MiB-25MiB"][0]
+    sizes = [sum(c["numel"][i] for i in b) * 4 for b in c["buckets"]]
+    assert sizes == [9446400] + [28351488] * 11 + [176446464]
+    assert oracle.bucket_assign([c["numel"][i] for i in c["order"]], [4] * len(c["order"]), c["limits"],
+                                tensor_indices=c["order"])[0] == c["buckets"]
     for k in want:
         assert abs(got[k] - want[k]) <= 2, (k, got[k])
 
