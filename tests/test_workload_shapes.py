@@ -27,3 +27,30 @@ def test_grad_ready_order_is_a_permutation():
         order = bench.grad_ready_order(n, cfg["layers"], cfg["tie"])
         assert sorted(order) == list(range(n)), wl
         assert order[-1] == 0          # the embedding's gradient is ready last
+
+
+def test_grad_ready_order_and_shapes_match_real_autograd():
+    """bench.py replays gradients in the order a real Llama backward makes them ready: checked here
+    against autograd itself on a 3-layer LlamaForCausalLM (tied and untied), together with the
+    parameter shape list in DDP registration order."""
+    import torch
+    from transformers import LlamaConfig, LlamaForCausalLM
+    for tie in (True, False):
+        cfg = LlamaConfig(hidden_size=64, num_hidden_layers=3, num_attention_heads=4, num_key_value_heads=2,
+                          intermediate_size=128, vocab_size=256, tie_word_embeddings=tie)
+        torch.manual_seed(0)
+        model = LlamaForCausalLM(cfg)
+        seen, params = set(), []
+        for _, mod in model.named_modules():
+            for _, p in mod.named_parameters(recurse=False):
+                if p not in seen:
+                    seen.add(p)
+                    params.append(p)
+        assert [tuple(p.shape) for p in params] == [tuple(s) for s in bench.llama_param_shapes(64, 3, 4, 2, 128, 256, tie)]
+        index = {id(p): i for i, p in enumerate(params)}
+        order = []
+        for p in params:
+            p.register_post_accumulate_grad_hook(lambda q: order.append(index[id(q)]))
+        ids = torch.randint(0, 256, (2, 16))
+        model(input_ids=ids, labels=ids).loss.backward()
+        assert order == bench.grad_ready_order(len(params), 3, tie), tie
