@@ -250,3 +250,55 @@ def _worker_compress_hook(rank, ws, port):
 
 def test_compress_comm_hook(native_lib):
     mp.spawn(_worker_compress_hook, args=(2, 29671), nprocs=2, join=True)
+
+
+def _worker_llama_layout(rank, ws, port):
+    """Rebuilt bucket layout on a model whose gradient-ready order is NOT the reversed registration
+    order (Llama: norm weights arrive out of line): ours equals what stock DDP's reducer builds,
+    bucket by bucket, parameter by parameter, offset by offset."""
+    _setup(rank, ws, port)
+    import copy
+    os.environ["HF_HUB_OFFLINE"] = "1"
+    from transformers import LlamaConfig, LlamaForCausalLM
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    torch.manual_seed(0)
+    cfg = LlamaConfig(hidden_size=32, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+                      intermediate_size=64, vocab_size=128, tie_word_embeddings=True)
+    base = LlamaForCausalLM(cfg)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, bucket_cap_mb=0.006)
+    ours = ddp_b200.DistributedDataParallel(b, bucket_cap_mb=0.006, kernels=OracleKernels())
+    pid = {id(p): i for i, p in enumerate(ref.module.parameters())}
+    seen = {}
+
+    def observe(state, bucket):
+        offs = [int((g.data_ptr() - bucket.buffer().data_ptr()) // 4) for g in bucket.gradients()]
+        seen.setdefault(state["it"], []).append((bucket.index(), [pid[id(p)] for p in bucket.parameters()], offs))
+        fut = dist.all_reduce(bucket.buffer().div_(ws), async_op=True).get_future()
+        return fut.then(lambda f: f.value()[0])
+
+    state = {"it": 0}
+    ref.register_comm_hook(state, observe)
+    for it in range(3):
+        state["it"] = it
+        g = torch.Generator().manual_seed(100 * it + rank)
+        ids = torch.randint(0, 128, (2, 8), generator=g)
+        for m in (ref, ours):
+            m.zero_grad()
+            m(input_ids=ids, labels=ids).loss.backward()
+        if it >= 1:
+            want = sorted(seen[it])
+            got = ours.bucket_layout()
+            assert [x[1] for x in want] == [bk["parameters"] for bk in got], it
+            assert [x[2] for x in want] == [bk["offsets"] for bk in got], it
+        for pr, po in zip(a.parameters(), b.parameters()):
+            assert torch.equal(pr.grad, po.grad), it
+    assert len(ours.bucket_layout()) > 3
+    ready = [pi for bk in ours.bucket_layout() for pi in bk["parameters"]]
+    assert ready != list(range(len(ready) - 1, -1, -1)), "this model was chosen because its ready order is not the reversed one"
+    dist.destroy_process_group()
+
+
+def test_rebuilt_layout_on_llama_matches_stock_ddp(native_lib):
+    mp.spawn(_worker_llama_layout, args=(2, 29681), nprocs=2, join=True)
