@@ -88,7 +88,8 @@ class DistributedDataParallel(nn.Module):
                  static_graph: bool = False, delay_all_reduce_named_params=None,
                  param_to_hook_all_reduce=None, mixed_precision=None, device_mesh=None,
                  skip_all_reduce_unused_params: bool = False, *, kernels=None,
-                 fused_allreduce: Optional[bool] = None, shard_optimizer: bool = False):
+                 fused_allreduce: Optional[bool] = None, shard_optimizer: bool = False,
+                 grad_bucket_dtype: Optional[torch.dtype] = None):
         super().__init__()
         if find_unused_parameters:
             raise NotImplementedError("ddp_b200: find_unused_parameters=True is outside the hot path covered")
@@ -155,6 +156,17 @@ class DistributedDataParallel(nn.Module):
         if self._zero and len({p.dtype for p in self._params}) != 1:
             raise NotImplementedError("ddp_b200 sharded update: parameters must share one dtype")
         self._param_sym = {}
+        # Buckets in a narrower dtype than the gradients (fp32 gradients -> bf16 buckets): the pack
+        # kernel scales and rounds once, round(fp32(g) * float(1/ws)), the collective moves half the
+        # bytes, the unpack kernel widens back into p.grad. torch's closest equivalent is
+        # bf16_compress_hook (default_hooks.py:57-134), which rounds first and divides afterwards.
+        self._bucket_dtype = grad_bucket_dtype
+        if grad_bucket_dtype is not None:
+            if grad_bucket_dtype not in (torch.bfloat16, torch.float32):
+                raise TypeError("grad_bucket_dtype must be torch.bfloat16 or torch.float32")
+            if gradient_as_bucket_view or self._zero:
+                raise ValueError("grad_bucket_dtype needs gradient_as_bucket_view=False and no shard_optimizer: "
+                                 "p.grad keeps the parameter dtype, so it cannot alias a bucket of another dtype")
         self._comm_hook: Optional[Callable] = None
         self._comm_hook_state = None
         self._hook_handles = []
@@ -264,7 +276,7 @@ class DistributedDataParallel(nn.Module):
         align = 128
         arena_len, starts = {}, []
         for spec in specs:
-            dt = self._params[spec.indices[0]].dtype
+            dt = self._bucket_dtype or self._params[spec.indices[0]].dtype
             off = (arena_len.get(dt, 0) + align - 1) // align * align
             starts.append(off)
             arena_len[dt] = off + spec.numel
@@ -278,7 +290,7 @@ class DistributedDataParallel(nn.Module):
             self._arenas = {dt: torch.zeros(max(n, 1), dtype=dt, device=self.device) for dt, n in arena_len.items()}
         first = 0
         for b, spec in enumerate(specs):
-            dt = self._params[spec.indices[0]].dtype
+            dt = self._bucket_dtype or self._params[spec.indices[0]].dtype
             buf = self._arenas[dt][starts[b]:starts[b] + spec.numel]
             views = [buf[o:o + numels[i]].view_as(self._params[i]) for i, o in zip(spec.indices, spec.offsets)]
             bk = _Bucket(b, spec, buf, views, first, [self._params[i] for i in spec.indices])
@@ -491,7 +503,9 @@ class DistributedDataParallel(nn.Module):
             dt = self._buckets[i].dtype
             grads = []
             taken = 0
-            while j < b1 and self._buckets[j].dtype == dt and (taken == 0 or taken + self._buckets[j].spec.numel <= budget):
+            pdt = self._buckets[i].params[0].dtype
+            while (j < b1 and self._buckets[j].dtype == dt and self._buckets[j].params[0].dtype == pdt
+                   and (taken == 0 or taken + self._buckets[j].spec.numel <= budget)):
                 taken += self._buckets[j].spec.numel
                 for p in self._buckets[j].params:
                     g = p.grad
@@ -733,7 +747,7 @@ class DistributedDataParallel(nn.Module):
             raise RuntimeError("ddp.clip_grad_norm_ needs a completed synchronised backward; "
                                "use ddp_b200.clip_grad_norm_(parameters, ...) otherwise")
         k = self._kernels
-        all_bf16 = all(bk.dtype == torch.bfloat16 for bk in self._buckets)
+        all_bf16 = all(p.dtype == torch.bfloat16 for p in self._params)      # the GRADIENT dtype decides, as in torch
         out = k.norm_finalize(self._sumsq, float(max_norm), torch_bf16=(torch_rounding and all_bf16),
                               out=self._norm_out)
         if error_if_nonfinite and not bool(torch.isfinite(out[0])):
@@ -752,4 +766,4 @@ class DistributedDataParallel(nn.Module):
                 tab = k.table([None, gl, None, None], [g.numel() for g in gl])
                 k.scale_by(tab, dt, coef, prefer_device=False)
         self._sumsq_valid = fused_optimizer is not None   # grads changed in place otherwise
-        return out[0].to(self._buckets[0].dtype)
+        return out[0].to(self._params[self._order[0]].dtype)

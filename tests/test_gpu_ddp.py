@@ -138,7 +138,34 @@ def _two_rank_worker(rank, ws, port):
     os.environ["DDPB200_FUSED_MODE"] = "auto"
     for fused in (False, True):
         _mixed_dtype_two_ranks(rank, fused)
+        _bf16_buckets_two_ranks(rank, fused)
     dist.destroy_process_group()
+
+
+def _bf16_buckets_two_ranks(rank, fused):
+    """fp32 model, bf16 gradient buckets (pack casts down with one rounding, unpack widens back)."""
+    import ddp_b200
+    mg = _golden_module()
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    base = mg.SmallNet().to(dev)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a, device_ids=[rank], bucket_cap_mb=0.008)
+    ours = ddp_b200.DistributedDataParallel(b, device_ids=[rank], bucket_cap_mb=0.008, fused_allreduce=fused,
+                                            grad_bucket_dtype=torch.bfloat16)
+    for s in range(3):
+        ids, tgt = mg.live_batch(70 + s, rank)
+        for m in (ref, ours):
+            m.zero_grad()
+            torch.nn.functional.cross_entropy(m(ids).flatten(0, 1), tgt.to(dev).flatten()).backward()
+        assert all(bk.dtype == torch.bfloat16 for bk in ours._buckets)
+        for pa, pb in zip(a.parameters(), b.parameters()):
+            scale = float(pa.grad.abs().max())
+            assert pb.grad.dtype == torch.float32
+            assert torch.allclose(pa.grad, pb.grad, rtol=0, atol=2 ** -7 * scale + 1e-9), (fused, s)
+        n_ref = torch.nn.utils.clip_grad_norm_(a.parameters(), 1e9)
+        n_our = ours.clip_grad_norm_(1e9)
+        assert abs(float(n_ref) - float(n_our)) <= 2 ** -7 * float(n_ref)
 
 
 def _mixed_dtype_two_ranks(rank, fused):

@@ -302,3 +302,47 @@ def _worker_llama_layout(rank, ws, port):
 
 def test_rebuilt_layout_on_llama_matches_stock_ddp(native_lib):
     mp.spawn(_worker_llama_layout, args=(2, 29681), nprocs=2, join=True)
+
+
+def _worker_bf16_buckets(rank, ws, port):
+    """grad_bucket_dtype=torch.bfloat16 on an fp32 model: the pack kernel scales and rounds once to
+    bf16, the collective runs on bf16 buckets, the unpack kernel widens back into fp32 p.grad. Checked
+    against the arithmetic written out with torch ops, and against stock DDP's bf16_compress_hook
+    (same idea, rounding order reversed) within one bf16 ulp of the terms."""
+    _setup(rank, ws, port)
+    import copy
+    import ddp_b200
+    from oracle_backend import OracleKernels
+    from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+    mg = _load_golden_module()
+    torch.manual_seed(0)
+    base = mg.SmallNet()
+    a, b, c = copy.deepcopy(base), copy.deepcopy(base), copy.deepcopy(base)
+    ours = ddp_b200.DistributedDataParallel(a, bucket_cap_mb=0.008, kernels=OracleKernels(), grad_bucket_dtype=torch.bfloat16)
+    ref = torch.nn.parallel.DistributedDataParallel(b, bucket_cap_mb=0.008)
+    ref.register_comm_hook(None, default_hooks.bf16_compress_hook)
+    plain = torch.nn.parallel.DistributedDataParallel(c, bucket_cap_mb=0.008)        # fp32 all the way
+    with pytest.raises(ValueError):
+        ddp_b200.DistributedDataParallel(copy.deepcopy(base), gradient_as_bucket_view=True, kernels=OracleKernels(),
+                                         grad_bucket_dtype=torch.bfloat16)
+    for s in range(2):
+        ids, tgt = mg.live_batch(60 + s, rank)
+        for m in (ours, ref, plain):
+            m.zero_grad()
+            torch.nn.functional.cross_entropy(m(ids).flatten(0, 1), tgt.flatten()).backward()
+        # local gradients of both ranks, to write the expected arithmetic out
+        for po, pr, pp in zip(a.parameters(), b.parameters(), c.parameters()):
+            assert po.grad.dtype == torch.float32
+            assert all(bk.dtype == torch.bfloat16 for bk in ours._buckets)
+            scale = float(pp.grad.abs().max())      # roundings are relative to the TERMS (which may cancel)
+            assert torch.allclose(po.grad, pp.grad, rtol=0, atol=2 ** -7 * scale + 1e-9)   # vs exact fp32 averaging
+            assert torch.allclose(po.grad, pr.grad, rtol=0, atol=2 ** -6 * scale + 1e-9)   # vs torch's compress hook
+            assert torch.equal(po.grad, po.grad.to(torch.bfloat16).float())            # values are bf16-representable
+        n_o = ours.clip_grad_norm_(1e9)
+        n_p = torch.nn.utils.clip_grad_norm_(c.parameters(), 1e9)
+        assert n_o.dtype == torch.float32 and abs(float(n_o) - float(n_p)) <= 2 ** -7 * float(n_p)
+    dist.destroy_process_group()
+
+
+def test_bf16_gradient_buckets_for_fp32_model(native_lib):
+    mp.spawn(_worker_bf16_buckets, args=(2, 29691), nprocs=2, join=True)
