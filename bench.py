@@ -205,6 +205,159 @@ def bind_to_gpu_numa_node(dev_index):
     return None
 
 
+# ---- N>1 self-check: the collective the step uses, against NCCL and across ranks -----------------------
+def _ulp_key(t):
+    """Monotonic integer key of a bf16/fp32 tensor's bit patterns (difference of keys = distance in ulps)."""
+    if t.dtype == torch.bfloat16:
+        b = t.view(torch.int16).to(torch.int32)
+        return torch.where(b < 0, -(b & 0x7fff), b)
+    b = t.view(torch.int32).to(torch.int64)
+    return torch.where(b < 0, -(b & 0x7fffffff), b)
+
+
+def _max_ulp(a, b, block=1 << 27):
+    worst = 0
+    for o in range(0, a.numel(), block):
+        worst = max(worst, int((_ulp_key(a[o:o + block]) - _ulp_key(b[o:o + block])).abs().max()))
+    return worst
+
+
+def parity_check(ddp, ws, rank, dev, zero1_too, shapes, order, cfg):
+    """Run BEFORE the timed loop on the real bucket arena of this run (multi-GPU gradients
+    are checked to a tolerance, everything replicated must be bit-identical):
+      (i)   the step's gradient collective (fused kernel with the scale it is given in the step, or NCCL)
+            against stock DDP's arithmetic — round(fp32(g) * float(1/ws)) per rank, then SUM — with the sum
+            taken by NCCL in fp32: within one rounding of the bucket dtype; and against NCCL's own
+            allreduce in the bucket dtype (reported, NCCL rounds at every hop);
+      (ii)  averaged gradients and per-tensor sums of squares bit-identical on all ranks;
+      (iii) sums of squares against a double-precision sum of what was stored, 3e-6 relative;
+      (iv)  sharded update (ZeRO-1 style): parameters after 2 steps bit-equal to the replicated path.
+    Every rank returns the same verdict."""
+    k = ddp._kernels
+    inv = ddp._inv_world_size
+    out = {"world": ws, "collective": "fused" if ddp._fused else "nccl"}
+    ok = True
+    worst_f32, worst_nccl, worst_rel, same = 0, 0, 0.0, True
+    arenas = ddp._sym if ddp._fused else {dt: None for dt in ddp._arenas}
+    for dt in arenas:
+        flat = ddp._arenas[dt]
+        rows = [bk for bk in ddp._buckets if bk.dtype == dt]
+        first, n = rows[0].first, sum(bk.n for bk in rows)
+        flat.normal_(0, 0.01, generator=torch.Generator(device=dev).manual_seed(1234 + rank))
+        pre = (flat.float() * inv).to(dt)                        # stock: bucket_view = grad * (1/ws), in the bucket dtype
+        ref32 = pre.float()
+        dist.all_reduce(ref32)                                   # SUM of the pre-scaled values, fp32 accumulation
+        want = ref32.to(dt)
+        del ref32
+        nccl = pre.clone()
+        dist.all_reduce(nccl)                                    # NCCL in the bucket dtype
+        ss = torch.empty(n, dtype=torch.float32, device=dev)
+        torch.cuda.synchronize()
+        if ddp._fused:
+            fold = ddp._folds_scale(dt)
+            if not fold:
+                flat.copy_(pre)
+            k.allreduce_sumsq(ddp._view_table, dt, ddp._sym[dt], ss, first=first, count=n, scatter=False,
+                              scale=inv if fold else 1.0)
+            out["scale_folded_into_collective"] = bool(fold)
+        else:
+            flat.copy_(pre)
+            dist.all_reduce(flat)
+            k.sumsq(ddp._view_table, dt, ss, first=first, count=n)
+        del pre
+        torch.cuda.synchronize()
+        worst_f32 = max(worst_f32, _max_ulp(flat, want))
+        worst_nccl = max(worst_nccl, _max_ulp(flat, nccl))
+        del want, nccl
+        views = [v for bk in rows for v in bk.views]
+        exact = torch.stack([v.double().pow(2).sum() for v in views])
+        rel = ((ss.double() - exact).abs() / exact.clamp_min(1e-300)).max()
+        worst_rel = max(worst_rel, float(rel))
+        twin = flat.clone()
+        dist.broadcast(twin, src=0)
+        same = same and torch.equal(twin.view(torch.int16 if dt == torch.bfloat16 else torch.int32),
+                                    flat.view(torch.int16 if dt == torch.bfloat16 else torch.int32))
+        del twin
+        ss0 = ss.clone()
+        dist.broadcast(ss0, src=0)
+        same = same and torch.equal(ss0.view(torch.int32), ss.view(torch.int32))
+    flag = torch.tensor([1 if same else 0, worst_f32, worst_nccl], dtype=torch.int64, device=dev)
+    dist.all_reduce(flag[:1], op=dist.ReduceOp.MIN)
+    dist.all_reduce(flag[1:], op=dist.ReduceOp.MAX)
+    relt = torch.tensor([worst_rel], dtype=torch.float64, device=dev)
+    dist.all_reduce(relt, op=dist.ReduceOp.MAX)
+    out["fused_vs_fp32sum_max_ulp" if ddp._fused else "nccl_vs_fp32sum_max_ulp"] = int(flag[1])
+    out["fused_vs_nccl_max_ulp" if ddp._fused else "nccl_vs_nccl_max_ulp"] = int(flag[2])
+    out["ranks_bit_identical"] = bool(int(flag[0]))
+    out["sumsq_rel"] = float(relt)
+    # one rounding of the bucket dtype for the fused kernel (one owner sums in fp32 and rounds once); NCCL's
+    # own algorithm may round at every hop, so the NCCL arm of this bench gets ws roundings
+    ok = ok and out["ranks_bit_identical"] and out["sumsq_rel"] <= 3e-6 and int(flag[1]) <= (1 if ddp._fused else ws)
+    if zero1_too:
+        try:
+            z = zero1_parity(shapes, order, dev, rank, ws)
+        except Exception as e:                                   # symmetric memory could not be set up: say so
+            z = {"zero1_bit_identical": None, "zero1_note": f"{type(e).__name__}: {str(e)[:160]}"}
+        out.update(z)
+        if z.get("zero1_bit_identical") is False:
+            ok = False
+    out["ok"] = bool(ok)
+    return out
+
+
+def zero1_parity(shapes, order, dev, rank, ws, steps=2):
+    """(iv): the sharded update next to the replicated path on twin copies of the full parameter set, same
+    rank-dependent synthetic gradients, both over the peer-memory transport (so that both sum in rank
+    order): parameters after `steps` steps must be the same bits."""
+    import ddp_b200
+    local = dev.index
+    dtype = torch.bfloat16
+    prev_mode = os.environ.get("DDPB200_FUSED_MODE")
+    os.environ["DDPB200_FUSED_MODE"] = "peer"       # read when an arena is created (also by the bucket rebuild below)
+    try:
+        return _zero1_parity(ddp_b200, shapes, order, dev, rank, local, dtype, steps)
+    finally:
+        if prev_mode is None:
+            os.environ.pop("DDPB200_FUSED_MODE", None)
+        else:
+            os.environ["DDPB200_FUSED_MODE"] = prev_mode
+
+
+def _zero1_parity(ddp_b200, shapes, order, dev, rank, local, dtype, steps):
+    mA, mB = ParamSet(shapes, dtype, dev, seed=3), ParamSet(shapes, dtype, dev, seed=3)
+    dA = ddp_b200.DistributedDataParallel(mA, device_ids=[local], gradient_as_bucket_view=True, fused_allreduce=True)
+    dB = ddp_b200.DistributedDataParallel(mB, device_ids=[local], gradient_as_bucket_view=True, fused_allreduce=True,
+                                          shard_optimizer=True)
+    oA = ddp_b200.AdamW(list(mA.parameters()), lr=LR, weight_decay=1e-2)
+    oB = ddp_b200.ShardedAdamW(dB, lr=LR, weight_decay=1e-2)
+    pA, pB = list(mA.parameters()), list(mB.parameters())
+    numel = [p.numel() for p in pA]
+    total = sum(numel)
+    same = True
+    for s in range(steps):
+        gflat = torch.empty(total, dtype=dtype, device=dev).normal_(
+            0, 0.01, generator=torch.Generator(device=dev).manual_seed(100 * s + 7 + rank))
+        gs, o = [], 0
+        for n_, sh in zip(numel, shapes):
+            gs.append(gflat[o:o + n_].view(sh))
+            o += n_
+        dA.reduce_gradients([g.clone() for g in gs], order=order if s == 0 else None)
+        dA.clip_grad_norm_(MAX_NORM, fused_optimizer=oA)
+        oA.step()
+        dB.reduce_gradients(gs)
+        dB.clip_grad_norm_(MAX_NORM, fused_optimizer=oB)
+        oB.step()
+        torch.cuda.synchronize()
+        same = same and all(torch.equal(a.view(torch.int16), b.view(torch.int16)) for a, b in zip(pA, pB))
+    changed = not torch.equal(pA[0], ParamSet(shapes[:1], dtype, dev, seed=3).ps[0])
+    flag = torch.tensor([1 if (same and changed) else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    del dA, dB, oA, oB, mA, mB
+    torch.cuda.empty_cache()
+    return {"zero1_bit_identical": bool(int(flag)), "zero1_steps": steps, "zero1_transport": "peer (both arms)"}
+
+
+
 # ---- our arm ------------------------------------------------------------------------------------
 def run_ours(args):
     import ddp_b200
@@ -264,15 +417,27 @@ def run_ours(args):
 
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
 
+    # N>1: after the rebuild the gradients LIVE in the bucket arena (gradient_as_bucket_view: p.grad is its
+    # bucket view, the producer writes there), so no pack launch is left and the 1/world_size scale rides in
+    # the collective. --separate-grads keeps them in a buffer of their own (pack = copy + scale per step).
+    in_arena = ws > 1 and not args.separate_grads
+    state = {"resident": False}
+
     def step(i=None, first=False):
-        ddp.reduce_gradients(grads, order=order if first else None)
+        if state["resident"]:
+            ddp.reduce_gradients(None)                 # p.grad already is the bucket view
+        else:
+            ddp.reduce_gradients(grads, order=order if first else None)
         ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
         if i is not None:
             ev[i][0].record()
         opt.step()
         if i is not None:
             ev[i][1].record()
-        opt.zero_grad()
+        if in_arena and ddp._has_rebuilt and not first:
+            state["resident"] = True                   # the arena keeps the (averaged) gradients: next step's input
+        else:
+            opt.zero_grad()
 
     def sync_all():
         torch.cuda.synchronize()
@@ -281,11 +446,16 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     step(first=True)                    # iteration 0: one bucket, records the ready order
+    step()                              # rebuilt buckets from here on
+    parity = None
+    if ws > 1 and not args.no_parity_check:
+        parity = parity_check(ddp, ws, rank, dev, zero1_too=not args.no_zero1_check, shapes=shapes,
+                              order=order, cfg=cfg)
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()                  # samples the same load from the warm-up on, through the timed region
     for _ in range(max(args.warmup, 3)):
-        step()                          # rebuilt buckets from here on
+        step()
     stats0 = dict(ddp._get_ddp_logging_data())
 
     # ---- timed: inputs resident in HBM -----------------------------------------------------------
@@ -352,6 +522,7 @@ def run_ours(args):
             if it + 1 < e2e_steps:
                 h2d(1 - slot)                                      # next step's gradients start moving now
             cur = torch.cuda.current_stream()
+            state["resident"] = False
             ddp.reduce_gradients(land_views[slot], before_bucket=lambda b, _idx: cur.wait_event(landed[slot][b]))
             ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
             norm_host2[slot].copy_(ddp._norm_out, non_blocking=True)
@@ -412,7 +583,12 @@ def run_ours(args):
             "path_bytes_per_step": {"pack": 0 if ws == 1 else 4 * total, "norm": 2 * total, "adamw": 14 * total},
             "path_gbs": ((0 if ws == 1 else 4 * total) + 2 * total + 14 * total) / (ms / args.steps * 1e-3) / 1e9,
             "clocks": clk, "total_norm": last_norm,
+            "gradients": ("resident in the bucket arena (p.grad is its bucket view): no pack launch, the 1/world_size "
+                          "scale is applied inside the collective") if in_arena and ddp._fused and stats1.get("folded_scale_launches", 0)
+                         else ("separate buffer: one pack (copy + scale) per step" if ws > 1 else "in place, nothing exchanged"),
         }
+        if parity is not None:
+            out["parity_check"] = parity
         if ws > 1:
             # bucket allreduce bus bandwidth, measured alone on the same buckets (NCCL-tests convention)
             out["allreduce"] = measure_allreduce(ddp, ws, dev)
@@ -423,8 +599,10 @@ def run_ours(args):
         os.sched_setaffinity(0, all_cpus)            # the CPU baseline gets every host core
         out["cpu_baseline"] = cpu_baseline_sample(cfg, total)
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        sys.exit(3)                                  # the launcher's exit code carries a failed self-check
 
 
 def measure_allreduce(ddp, ws, dev):
@@ -468,8 +646,16 @@ def measure_allreduce(ddp, ws, dev):
                 k.allreduce_sumsq(tab, bk_dt, arena, ss[first:first + n], first=first, count=n, scatter=False)
         if len(ddp._sym) == 1:
             ms_f = timed(run_fused)
+            mc = any(a.use_multicast for a in ddp._sym.values())
+            # bytes one GPU really moves per NVLink direction: multicast (1 + 1/n) S (its copy is read once by
+            # the switch + it stores its 1/n through the switch), peer 2(n-1)/n S (as a ring)
+            wire = Sa * ((1 + 1 / ws) if mc else 2 * (ws - 1) / ws)
             fused = {"ms": ms_f, "busbw_equiv_gbs": Sa / (ms_f * 1e-3) * 2 * (ws - 1) / ws / 1e9,
-                     "mode": "multicast" if any(a.use_multicast for a in ddp._sym.values()) else "peer",
+                     "busbw_convention": "NCCL-tests ring equivalent, S/t * 2(n-1)/n",
+                     "wire_gbs_per_direction": wire / (ms_f * 1e-3) / 1e9,
+                     "wire_bytes_per_direction": wire, "wire_frac_of_900_nominal": wire / (ms_f * 1e-3) / 1e9 / 900.0,
+                     "wire_frac_of_770_measured_peer_copy": wire / (ms_f * 1e-3) / 1e9 / 770.0,
+                     "mode": "multicast" if mc else "peer",
                      "includes": "allreduce + per-tensor sum of squares + 2 barriers + fold"}
     for a in arenas:
         a.zero_()
@@ -573,6 +759,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to its GPU's NUMA-local CPUs")
     ap.add_argument("--skip-e2e", action="store_true", help="skip the host-gradient leg (large workloads: pinned host memory)")
+    ap.add_argument("--separate-grads", action="store_true",
+                    help="N>1: keep the synthetic gradients in a buffer of their own (one pack launch per step) instead "
+                         "of in the bucket arena")
+    ap.add_argument("--no-parity-check", action="store_true", help="N>1: skip the self-check before the timed loop")
+    ap.add_argument("--no-zero1-check", action="store_true", help="N>1: skip part (iv) of the self-check (sharded update)")
     ap.add_argument("--zero1", action="store_true",
                     help="N>1: the sharded update (reduce-scatter + AdamW on owned chunks + all-gather of parameters) "
                          "instead of the drop-in replicated path; an extension, not the default")

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_PKG, "libddp_b200.so")
 CSRC = os.path.join(_PKG, "csrc")
 HEADER = os.path.join(os.path.dirname(_PKG), "include", "ddp_b200.h")
 
+ABI_VERSION = 2
 F32, BF16 = 0, 1
 TABLE_HOST, TABLE_DEVICE = 0, 1
 NORM_EXACT_F32, NORM_TORCH_BF16 = 0, 1
@@ -57,11 +58,14 @@ SIGNATURES = {
     "ddpb200_fused_clip_adamw": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _f64, _vp,
                                                 _f64, _f64, _f64, _f64, _i64, _vp, _vp, _vp, _u32, _vp]),
     "ddpb200_adamw_bias_corrections": (ctypes.c_int, [_f64, _f64, _i64, _vp]),
-    "ddpb200_allreduce_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _vp]),
+    "ddpb200_allreduce_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _vp]),
     "ddpb200_fold_chunk_partials": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
-    "ddpb200_reduce_scatter_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _vp]),
+    "ddpb200_reduce_scatter_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _vp]),
     "ddpb200_sharded_adamw_allgather": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _f64, _vp,
                                                        _f64, _f64, _f64, _f64, _i64, _vp, _u32, _i32, _vp]),
+    "ddpb200_selfcheck_sqrt": (ctypes.c_int, [_u32, ctypes.c_uint64, _f32, _f32, _vp, _vp]),
+    "ddpb200_selfcheck_div": (ctypes.c_int, [ctypes.c_uint64, ctypes.c_uint64, _vp, _vp]),
+    "ddpb200_selfcheck_div_by_const": (ctypes.c_int, [_vp, _i32, _vp, _vp]),
 }
 
 
@@ -92,7 +96,7 @@ def lib() -> ctypes.CDLL:
             fn = getattr(L, name)  # AttributeError here = header and library disagree
             fn.restype = res
             fn.argtypes = args
-        if L.ddpb200_abi_version() != 1:
+        if L.ddpb200_abi_version() != ABI_VERSION:
             raise RuntimeError("libddp_b200.so ABI version mismatch")
         _lib = L
     return _lib

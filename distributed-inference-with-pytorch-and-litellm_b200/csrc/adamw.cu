@@ -25,9 +25,10 @@ namespace ddpb200 {
 
 // One chunk through G-element groups (vector accesses); returns how many elements were done, the
 // ragged end is left to the caller's scalar loop.
-template <int PDT, int GDT, int SDT, int MODE, int VECB>
+template <int PDT, int GDT, int SDT, int MODE, int VECB, bool PACKED>
 __device__ __forceinline__ int64_t adamw_chunk_vec(char* P, char* Gp, char* M, char* V, int64_t len,
-                                                   const AdamScalars& a, const AdamRuntime& r, bool store_g) {
+                                                   const AdamScalars& a, const AdamRuntime& r,
+                                                   const AdamPacked& pk, bool store_g) {
   constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
   constexpr int G = GroupSize<VECB, any_f32>::G;
   const int64_t groups_end = len / G * G;
@@ -38,8 +39,12 @@ __device__ __forceinline__ int64_t adamw_chunk_vec(char* P, char* Gp, char* M, c
     GroupIO<PDT, G>::load(P, i, p);
     GroupIO<SDT, G>::load(M, i, m);
     GroupIO<SDT, G>::load(V, i, v);
+    if constexpr (PACKED && MODE != kModeGeneral) {
+      adamw_group_packed<GDT, MODE, G>(p, g, m, v, a, r, pk);
+    } else {
 #pragma unroll
-    for (int k = 0; k < G; ++k) adamw_elem<GDT, MODE>(p[k], g[k], m[k], v[k], a, r);
+      for (int k = 0; k < G; ++k) adamw_elem<GDT, MODE>(p[k], g[k], m[k], v[k], a, r);
+    }
     GroupIO<PDT, G>::store(P, i, p);
     GroupIO<SDT, G>::store(M, i, m);
     GroupIO<SDT, G>::store(V, i, v);
@@ -55,7 +60,7 @@ __device__ __forceinline__ bool all_aligned(const void* P, const void* Gp, const
 }
 
 // MAXVEC: widest access the kernel may use (32 = 256-bit, 16 = 128-bit: fewer live registers)
-template <class Tab, int PDT, int GDT, int SDT, int MODE, int CT, int MAXVEC = 32>
+template <class Tab, int PDT, int GDT, int SDT, int MODE, int CT, int MAXVEC = 32, bool PACKED = true>
 __global__ void __launch_bounds__(kThreads, CT)
 adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
              AdamScalars a, const float* __restrict__ lr_ptr, const float* __restrict__ clip_ptr,
@@ -65,11 +70,13 @@ adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chun
   if (found_inf_ptr && __ldg(found_inf_ptr) == 1.0f) return;      // GradScaler skip (cuh:137-139)
   const AdamRuntime r = make_adam_runtime(a, lr_ptr, clip_ptr, grad_scale_ptr, flags);
   const bool store_g = (flags & DDPB200_ADAMW_STORE_GRAD) != 0;
+  const AdamPacked pk = make_adam_packed(a, r);
   const int64_t chunk_base = tab.begin(0);
 
+  SegCursor cur;
   for (int64_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
-    const int s = find_seg(tab, c + chunk_base);
-    const int64_t start = (c + chunk_base - tab.begin(s)) * chunk_elems;
+    const int s = find_seg_cached(tab, c + chunk_base, chunk_base + total_chunks, cur);
+    const int64_t start = (c + chunk_base - cur.b) * chunk_elems;
     const int64_t rest = tab.numel(s) - start;
     const int64_t len = rest < chunk_elems ? rest : chunk_elems;
     char* P = static_cast<char*>(tab.ptr(s, 0)) + start * ElemOf<PDT>::size;
@@ -79,9 +86,9 @@ adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chun
 
     int64_t done = 0;
     if (MAXVEC >= 32 && all_aligned<PDT, GDT, SDT, GroupSize<32, any_f32>::G>(P, Gp, M, V))
-      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 32>(P, Gp, M, V, len, a, r, store_g);
+      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 32, PACKED>(P, Gp, M, V, len, a, r, pk, store_g);
     else if (all_aligned<PDT, GDT, SDT, GroupSize<16, any_f32>::G>(P, Gp, M, V))
-      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 16>(P, Gp, M, V, len, a, r, store_g);
+      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 16, PACKED>(P, Gp, M, V, len, a, r, pk, store_g);
     // ragged end, or a segment whose base is not even 16-byte aligned (odd offset inside a bucket)
     for (int64_t i = done + threadIdx.x; i < len; i += kThreads) {
       float p = load1<PDT>(P, i), g = load1<GDT>(Gp, i), m = load1<SDT>(M, i), v = load1<SDT>(V, i);
@@ -125,6 +132,16 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
         if (wide) {
           const int64_t wcap = (int64_t)sms * 3;
           adamw_kernel<Tab, PDT, GDT, SDT, MODE, 3, 32><<<(int)(chunks < wcap ? chunks : wcap), kThreads, 0, st>>>(
+              tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
+          return (int)cudaGetLastError();
+        }
+      }
+      // A/B switch for tools/kbench.py only: DDPB200_ADAMW_PACKED=0 selects the scalar element arithmetic
+      // (IEEE intrinsics per element) that round 1 shipped, for the all-bf16 fast modes
+      static const bool scalar_math = [] { const char* e = getenv("DDPB200_ADAMW_PACKED"); return e && atoi(e) == 0; }();
+      if constexpr (narrow) {
+        if (scalar_math) {
+          adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT, MAXVEC, false><<<grid, kThreads, 0, st>>>(
               tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
           return (int)cudaGetLastError();
         }

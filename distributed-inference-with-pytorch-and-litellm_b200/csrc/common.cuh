@@ -54,6 +54,20 @@ __device__ __forceinline__ int find_seg(const Tab& tab, int64_t c) {
   return lo;
 }
 
+// A CTA's chunks come c, c+grid, c+2*grid, ...: with chunks much shorter than the large tensors, the next
+// chunk is usually in the segment of the last one (or the following segment), so the binary search is
+// only taken when this cheap test fails. cur.s < 0 = nothing cached yet.
+struct SegCursor { int s = -1; int64_t b = 0, e = 0; };   // segment s covers absolute chunks [b, e)
+template <class Tab>
+__device__ __forceinline__ int find_seg_cached(const Tab& tab, int64_t c_abs, int64_t end_abs, SegCursor& cur) {
+  if (cur.s < 0 || c_abs < cur.b || c_abs >= cur.e) {
+    cur.s = find_seg(tab, c_abs);
+    cur.b = tab.begin(cur.s);
+    cur.e = (cur.s + 1 < tab.n) ? tab.begin(cur.s + 1) : end_abs;
+  }
+  return cur.s;
+}
+
 // ---- element types -----------------------------------------------------------------
 template <int DT> struct ElemOf;
 template <> struct ElemOf<DDPB200_F32>  { using type = float;          static constexpr int size = 4; };

@@ -29,6 +29,7 @@ sharded_adamw_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, co
   // (two 16-byte halves of a 32-byte group per lane measured 3x slower: half-filled NVLink packets)
   constexpr int G = (MC ? 16 : 32) / ES;
   const AdamRuntime r = make_adam_runtime(a, lr_ptr, clip_ptr, nullptr, flags);
+  const AdamPacked pk = make_adam_packed(a, r);
   const int64_t chunk_base = tab.begin(0);
   const int world = pp.world;
   char* const param_local = pp.arena[pp.rank];
@@ -56,8 +57,12 @@ sharded_adamw_kernel(DevTable tab, int64_t total_chunks, int64_t chunk_elems, co
         GroupIO<DT, G>::load(P, i, p);
         GroupIO<DT, G>::load(M, i, m);
         GroupIO<DT, G>::load(V, i, v);
+        if constexpr (MODE != kModeGeneral) {
+          adamw_group_packed<DT, MODE, G>(p, g, m, v, a, r, pk);
+        } else {
 #pragma unroll
-        for (int k = 0; k < G; ++k) adamw_elem<DT, MODE>(p[k], g[k], m[k], v[k], a, r);
+          for (int k = 0; k < G; ++k) adamw_elem<DT, MODE>(p[k], g[k], m[k], v[k], a, r);
+        }
         GroupIO<DT, G>::store(M, i, m);
         GroupIO<DT, G>::store(V, i, v);
         if constexpr (MC) {                                   // the switch replicates the store to every rank

@@ -49,9 +49,10 @@ stream_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chu
   if constexpr (DEVSCALE) scale = __ldg(scale_ptr);
   const int64_t chunk_base = tab.begin(0);
 
+  SegCursor cur;
   for (int64_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
-    const int s = find_seg(tab, c + chunk_base);
-    const int64_t start = (c + chunk_base - tab.begin(s)) * chunk_elems;
+    const int s = find_seg_cached(tab, c + chunk_base, chunk_base + total_chunks, cur);
+    const int64_t start = (c + chunk_base - cur.b) * chunk_elems;
     const int64_t rest = tab.numel(s) - start;
     const int64_t len = rest < chunk_elems ? rest : chunk_elems;
     const char* src = static_cast<const char*>(tab.ptr(s, SRC)) + start * ElemOf<SDT>::size;

@@ -178,6 +178,8 @@ class DistributedDataParallel(nn.Module):
         self._sumsq_valid = False
         self._coalesce = False
         self._coalesce_groups = int(os.environ.get("DDPB200_COALESCE_GROUPS", "4"))
+        # gradients that already live in the bucket arena: skip the in-place pack, scale inside the collective
+        self._fold_ok = os.environ.get("DDPB200_FOLD_SCALE", "1") == "1"
         self._stats = {"iterations": 0, "pack_launches": 0, "allreduces": 0, "norm_launches": 0,
                        "unpack_launches": 0, "rebuilt_bucket_sizes": []}
 
@@ -328,6 +330,7 @@ class DistributedDataParallel(nn.Module):
         # norm / in-place clip over the bucket views: static pointers -> device-resident table
         self._view_table = k.table([None, all_views, None, None], onum, chunk_elems=self._pack_table.chunk_elems,
                                    device=self.device if self._cuda else None)
+        self._view_ptrs = [v.data_ptr() for v in all_views]
         self._sumsq = torch.zeros(n, dtype=torch.float32, device=self.device)
         for bk in self._buckets:
             bk.sumsq = self._sumsq[bk.first:bk.first + bk.n]
@@ -487,6 +490,24 @@ class DistributedDataParallel(nn.Module):
             for b in range(b0, b1):
                 self._launch_bucket(self._buckets[b])
 
+    def _folds_scale(self, dt) -> bool:
+        """Whether the 1/world_size scale is applied INSIDE the fused collective for buckets of dtype dt.
+        A property of the configuration, identical on every rank (the owner of a chunk applies one scale
+        to every rank's copy, so the ranks must agree): fused collective, gradient_as_bucket_view, no
+        comm hook. Then a gradient that already IS its bucket view (accumulated in place by autograd, or
+        written there by the caller) needs no pack launch at all — stock DDP would still run the in-place
+        `bucket_view.div_(world_size)` (reducer.hpp:276) — and one that is not is copied unscaled.
+        Peer mode scales per rank before the sum (the bits a pack would have stored, any world size);
+        multicast mode scales the switch's sum, the same number only for a power-of-two world size
+        (csrc/fused_allreduce.cu), so it folds only then."""
+        if not (self._fused and self._comm_hook is None and self._fold_ok and self.gradient_as_bucket_view):
+            return False
+        return not (self._sym[dt].use_multicast and (self.world_size & (self.world_size - 1)))
+
+    def _aliased(self, first: int, grads: List[torch.Tensor]) -> bool:
+        vp = self._view_ptrs
+        return all(g.data_ptr() == vp[first + i] for i, g in enumerate(grads))
+
     def _launch_coalesced(self, b0: int, b1: int) -> None:
         """Buckets b0..b1-1 are complete AT ONCE and every rank knows it (manual gradient feed): per
         run of equal dtype ONE pack launch, ONE allreduce over the contiguous arena range, ONE norm
@@ -496,7 +517,14 @@ class DistributedDataParallel(nn.Module):
         # Up to `_coalesce_groups` sub-runs of about equal size: the pack of sub-run g+1 (HBM-bound,
         # compute stream) overlaps the collective of sub-run g (NVLink-bound, side stream).
         total = sum(bk.spec.numel for bk in self._buckets[b0:b1])
-        budget = max(1, -(-total // max(1, self._coalesce_groups)))
+        groups = self._coalesce_groups
+        if all(self._folds_scale(bk.dtype) for bk in self._buckets[b0:b1]):
+            # nothing to pack if the gradients are the bucket views: no pack to overlap, one collective per dtype
+            vp = self._view_ptrs
+            if all(p.grad is not None and p.grad.data_ptr() == vp[bk.first + i]
+                   for bk in self._buckets[b0:b1] for i, p in enumerate(bk.params)):
+                groups = 1
+        budget = max(1, -(-total // max(1, groups)))
         i = b0
         while i < b1:
             j = i
@@ -522,9 +550,12 @@ class DistributedDataParallel(nn.Module):
             first, n = self._buckets[i].first, len(grads)
             last = self._buckets[j - 1]
             span = self._arenas[dt][self._buckets[i].arena_start:last.arena_start + last.spec.numel]
-            self._pack_table.host["ptr"][first:first + n, 0] = [g.data_ptr() for g in grads]
-            k.pack(self._pack_table, gdt, dt, self._inv_world_size, first=first, count=n, prefer_device=False)
-            self._stats["pack_launches"] += 1
+            fold = self._folds_scale(dt)
+            if not (fold and gdt == dt and self._aliased(first, grads)):
+                self._pack_table.host["ptr"][first:first + n, 0] = [g.data_ptr() for g in grads]
+                k.pack(self._pack_table, gdt, dt, 1.0 if fold else self._inv_world_size, first=first, count=n,
+                       prefer_device=False)
+                self._stats["pack_launches"] += 1
 
             def behind():
                 if self.gradient_as_bucket_view:
@@ -541,7 +572,7 @@ class DistributedDataParallel(nn.Module):
                 ev.record()
                 with torch.cuda.stream(self._comm_stream):
                     self._comm_stream.wait_event(ev)
-                    self._fused_reduce(dt, gdt, first, n, grads)
+                    self._fused_reduce(dt, gdt, first, n, grads, self._inv_world_size if fold else 1.0)
             elif self._cuda:
                 ev = torch.cuda.Event()
                 ev.record()
@@ -609,12 +640,14 @@ class DistributedDataParallel(nn.Module):
         for g in grads:
             if g.dtype != gdt:
                 raise RuntimeError("ddp_b200: gradients of one bucket must share a dtype")
-        self._pack_table.host["ptr"][first:first + n, 0] = [g.data_ptr() for g in grads]
         hooked = self._comm_hook is not None
         # no hook: pre-divide, then SUM (div_factor_, reducer.hpp:497-500). With a hook the hook divides.
         scale = 1.0 if hooked else self._inv_world_size
-        k.pack(self._pack_table, gdt, bk.dtype, scale, first=first, count=n, prefer_device=False)
-        self._stats["pack_launches"] += 1
+        fold = self._folds_scale(bk.dtype)
+        if not (fold and gdt == bk.dtype and self._aliased(first, grads)):
+            self._pack_table.host["ptr"][first:first + n, 0] = [g.data_ptr() for g in grads]
+            k.pack(self._pack_table, gdt, bk.dtype, 1.0 if fold else scale, first=first, count=n, prefer_device=False)
+            self._stats["pack_launches"] += 1
         if hooked:
             gb = GradBucket(bk.index, bk.buffer, list(bk.views), list(bk.params), bk.index == len(self._buckets) - 1)
             bk.future = self._comm_hook(self._comm_hook_state, gb)
@@ -625,7 +658,7 @@ class DistributedDataParallel(nn.Module):
             ev.record()
             with torch.cuda.stream(self._comm_stream):
                 self._comm_stream.wait_event(ev)
-                self._fused_reduce(bk.dtype, gdt, first, n, grads)
+                self._fused_reduce(bk.dtype, gdt, first, n, grads, scale if fold else 1.0)
         elif self._cuda:
             ev = torch.cuda.Event()
             ev.record()
@@ -639,13 +672,15 @@ class DistributedDataParallel(nn.Module):
             self._after_reduce(bk, grads)
         self._stats["allreduces"] += 1
 
-    def _fused_reduce(self, dt, gdt, first: int, n: int, grads: List[torch.Tensor]) -> None:
+    def _fused_reduce(self, dt, gdt, first: int, n: int, grads: List[torch.Tensor], scale: float = 1.0) -> None:
         """Rows [first, first+n) of the arena: SUM over ranks in place + per-tensor sums of squares in
         one kernel over NVLink peer memory (csrc/fused_allreduce.cu), then the copy back into p.grad
         unless gradients are bucket views."""
         k = self._kernels
         k.allreduce_sumsq(self._view_table, dt, self._sym[dt], self._sumsq[first:first + n], first=first, count=n,
-                          scatter=self._zero)
+                          scatter=self._zero, scale=scale)
+        if scale != 1.0:
+            self._stats["folded_scale_launches"] = self._stats.get("folded_scale_launches", 0) + 1
         self._stats["fused_allreduces"] = self._stats.get("fused_allreduces", 0) + 1
         if not self.gradient_as_bucket_view:
             self._unpack_table.host["ptr"][first:first + n, 1] = [g.data_ptr() for g in grads]

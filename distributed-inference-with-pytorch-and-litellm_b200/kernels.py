@@ -232,11 +232,13 @@ class CudaKernels:
 
     # ---- fused bucket allreduce + norm over peer memory ---------------------------------------
     def allreduce_sumsq(self, tab: SegTable, dtype: torch.dtype, arena, sumsq_out: torch.Tensor,
-                        first: int = 0, count: Optional[int] = None, scatter: bool = False) -> None:
+                        first: int = 0, count: Optional[int] = None, scatter: bool = False,
+                        scale: float = 1.0) -> None:
         """SUM over ranks of rows [first, first+count) of the symmetric bucket arena, in place on
         every rank, and their per-tensor sums of squares into sumsq_out — barrier, one kernel,
         barrier, fold; all on the current stream. scatter=True: reduce-scatter only (the owner of
-        a chunk keeps the reduced values to itself), for the sharded update."""
+        a chunk keeps the reduced values to itself), for the sharded update. scale != 1 folds the
+        1/world_size of a skipped in-place pack into the kernel (see include/ddp_b200.h)."""
         if tab.dev is None:
             raise RuntimeError("allreduce_sumsq needs the device-resident table of bucket views")
         ptr, _, n, chunks = tab.args(first, count, True)
@@ -247,7 +249,7 @@ class CudaKernels:
         pm = arena.peer_map(chunk_off)
         fn = L.ddpb200_reduce_scatter_sumsq_chunks if scatter else L.ddpb200_allreduce_sumsq_chunks
         _lib.check(fn(ptr, n, chunks, tab.chunk_elems, dtype_code(dtype), ctypes.addressof(pm),
-                      int(arena.use_multicast), st), "ddpb200_allreduce_sumsq_chunks")
+                      int(arena.use_multicast), float(scale), st), "ddpb200_allreduce_sumsq_chunks")
         arena.barrier()                                   # every rank has written its chunks everywhere
         _lib.check(L.ddpb200_fold_chunk_partials(ptr, n, chunks, arena.partials.data_ptr() + 4 * chunk_off,
                                                  sumsq_out.data_ptr(), st), "ddpb200_fold_chunk_partials")

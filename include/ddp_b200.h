@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define DDPB200_ABI_VERSION 1
+#define DDPB200_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define DDPB200_API __attribute__((visibility("default")))
@@ -182,6 +182,11 @@ DDPB200_API int ddpb200_scale_by_device_scalar(const ddpb200_seg* table, int32_t
  * c % world and written to all ranks; its sum of squares is written to partials[p][c] on all ranks.
  * use_multicast != 0: multimem.ld_reduce / multimem.st through the switch ((1+1/n)*S NVLink bytes per
  * GPU and direction); 0: 256-bit peer loads and stores (2(n-1)/n*S), fp32 sum in rank order.
+ * scale folds the pack pass's 1/world_size in for gradients that already live in the arena
+ * (gradient_as_bucket_view: the in-place `bucket_view.div_(world_size)` of reducer.hpp:276 is then not
+ * launched at all): peer mode rounds fp32(g)*scale to the bucket dtype per rank before the sum — the
+ * bits a separate pack would have stored, for any world size; multicast mode scales the switch's sum,
+ * which is the same number only for a power-of-two scale and outside subnormals. scale = 1 otherwise.
  * The CALLER orders the ranks: a barrier after every rank has packed and before this call, and a
  * barrier after it before anyone reads the arena or the partials (then ddpb200_fold_chunk_partials
  * gives sumsq_out[n], bitwise identical on every rank). */
@@ -196,7 +201,7 @@ typedef struct ddpb200_peer_map {
 DDPB200_API int ddpb200_allreduce_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
                                                int64_t chunk_elems, int32_t dtype,
                                                const ddpb200_peer_map* peers, int32_t use_multicast,
-                                               void* stream);
+                                               float scale, void* stream);
 DDPB200_API int ddpb200_fold_chunk_partials(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
                                             const float* chunk_partials, float* sumsq_out, void* stream);
 
@@ -206,7 +211,7 @@ DDPB200_API int ddpb200_fold_chunk_partials(const ddpb200_seg* dev_table, int64_
 DDPB200_API int ddpb200_reduce_scatter_sumsq_chunks(const ddpb200_seg* dev_table, int64_t n, int64_t total_chunks,
                                                     int64_t chunk_elems, int32_t dtype,
                                                     const ddpb200_peer_map* peers, int32_t use_multicast,
-                                                    void* stream);
+                                                    float scale, void* stream);
 
 /* ---- §8e/§8f-4  sharded update: AdamW on the owned chunks + all-gather of the parameters -----------
  * ZeRO-1-style extension of a-6 (no counterpart in the reference; the replicated path above is the
@@ -251,6 +256,21 @@ DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, int32_t table
  * power taken in double on the host and rounded once
  * (TORCH/include/ATen/native/cuda/fused_adam_utils.cuh:131-150). */
 DDPB200_API int ddpb200_adamw_bias_corrections(double beta1, double beta2, int64_t step, float* out);
+
+/* ---- self-checks of the hand-written arithmetic (diagnostics; no counterpart in the reference) -----
+ * The fast modes of ddpb200_fused_clip_adamw write sqrt.rn and div.rn out as MUFU + packed f32x2 steps
+ * (csrc/adamw_math.cuh) and divide by sqrt(bc2) with a reciprocal + residual (csrc/common.cuh). These
+ * run the written-out forms beside the IEEE intrinsics on the device and count differing results:
+ * out3[0] = number of mismatches, out3[1..2] = the first offending input (zero out3 before the call).
+ *   _sqrt          every float bit pattern in [first_bits, first_bits+count) as v (stay below 2^20 =
+ *                  0x49800000, the box); with c > 0 also the whole denominator sqrt(v)/c + eps
+ *   _div           count pseudo-random (p, a, b) triples spread over the box, p - a/b
+ *   _div_by_const  every significand of x in [1,2) for each of the n constants (device array) */
+DDPB200_API int ddpb200_selfcheck_sqrt(uint32_t first_bits, uint64_t count, float c, float eps,
+                                       unsigned long long* out3, void* stream);
+DDPB200_API int ddpb200_selfcheck_div(uint64_t seed, uint64_t count, unsigned long long* out3, void* stream);
+DDPB200_API int ddpb200_selfcheck_div_by_const(const float* constants, int32_t n, unsigned long long* out3,
+                                               void* stream);
 
 #ifdef __cplusplus
 }

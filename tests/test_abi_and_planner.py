@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol(native_lib):
     for name in sorted(declared):
         assert hasattr(raw, name), f"{name} declared in include/ddp_b200.h but not exported"
     assert declared == set(_lib.SIGNATURES), "python binding and header disagree"
-    assert native_lib.ddpb200_abi_version() == 1
+    assert native_lib.ddpb200_abi_version() == _lib.ABI_VERSION == 2
     assert native_lib.ddpb200_error_string(0) == b"ok"
     assert b"invalid" in native_lib.ddpb200_error_string(-1)
 

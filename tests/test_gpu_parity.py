@@ -350,3 +350,99 @@ def test_full_size_properties_llama_1b_shapes(K, golden_dir):
     for step in (1, 2):
         oracle.fused_clip_adamw(pn, gn, mn, vn, step=step, clip_coef=0.5, **HP)
     assert bits_equal(p1[w], pn) and bits_equal(m1[w], mn) and bits_equal(v1[w], vn)
+
+
+# ---- the packed (f32x2) fast path of kernel (c): written-out sqrt / division vs the IEEE intrinsics -------
+def _selfcheck(fn, *args):
+    out = torch.zeros(3, dtype=torch.int64, device=DEV)
+    ddp_b200._lib.check(fn(*args, out.data_ptr(), torch.cuda.current_stream().cuda_stream), fn.__name__)
+    torch.cuda.synchronize()
+    return [int(x) for x in out.tolist()]
+
+
+def test_packed_sqrt_matches_ieee_over_the_whole_box(K):
+    """Every float v in [0, 2^20) — zero and all denormals included — through the written-out square root
+    (MUFU.RSQ + packed refinement on v*2^48), and through the whole denominator sqrt(v)/c + eps for the
+    bias corrections of a few steps: bit-identical to __fsqrt_rn / div_by_const / __fadd_rn."""
+    L = ddp_b200._lib.lib()
+    box_end = 0x49800000                                    # 2^20
+    bad = _selfcheck(L.ddpb200_selfcheck_sqrt, 0, box_end, -1.0, 0.0)
+    assert bad[0] == 0, f"sqrt mismatches: {bad[0]}, first v bits {bad[1]:#x} -> {bad[2]:#x}"
+    bc = np.zeros(2, dtype=np.float32)
+    for beta2, step, eps in ((0.999, 1, 1e-8), (0.999, 7, 1e-8), (0.95, 3, 1e-6), (0.999, 100000, 1e-12), (0.99, 20, 1.0)):
+        L.ddpb200_adamw_bias_corrections(0.9, beta2, step, bc.ctypes.data)
+        for first, count in ((0, 1 << 26), (0x2f000000, 1 << 27), (0x45000000, box_end - 0x45000000)):
+            bad = _selfcheck(L.ddpb200_selfcheck_sqrt, first, count, float(bc[1]), eps)
+            assert bad[0] == 0, f"denominator mismatches for c={bc[1]} eps={eps}: {bad}"
+
+
+def test_packed_division_matches_ieee_over_the_box(K):
+    """2^32 pseudo-random (p, a, b) over the packed path's box (a: zero, denormal, up to 2^20; b in
+    [2^-40, 2^21); |p| >= 2^-100): p - a/b as written out equals __fsub_rn(p, __fdiv_rn(a, b))."""
+    L = ddp_b200._lib.lib()
+    for seed in (1, 0x5eed5eed):
+        bad = _selfcheck(L.ddpb200_selfcheck_div, seed, 1 << 31)
+        assert bad[0] == 0, f"division mismatches: {bad[0]}, first (a,b) bits {bad[1]:#x}, p bits {bad[2]:#x}"
+
+
+def test_div_by_const_matches_ieee_for_every_step(K):
+    """div_by_const(x, c, RN(1/c)) == __fdiv_rn(x, c) for EVERY significand of x and every divisor
+    c = sqrt(1 - beta2^t) the kernel can meet in t = 1..20000 for beta2 in {0.999, 0.99, 0.95}."""
+    L = ddp_b200._lib.lib()
+    cs = set()
+    bc = np.zeros(2, dtype=np.float32)
+    for beta2 in (0.999, 0.99, 0.95):
+        for step in range(1, 20001):
+            L.ddpb200_adamw_bias_corrections(0.9, beta2, step, bc.ctypes.data)
+            cs.add(float(bc[1]))
+            if bc[1] == 1.0:
+                break
+    cs = torch.tensor(sorted(cs), dtype=torch.float32, device=DEV)
+    assert cs.numel() > 10000
+    out = torch.zeros(3, dtype=torch.int64, device=DEV)
+    ddp_b200._lib.check(L.ddpb200_selfcheck_div_by_const(cs.data_ptr(), cs.numel(), out.data_ptr(),
+                                                         torch.cuda.current_stream().cuda_stream), "selfcheck")
+    torch.cuda.synchronize()
+    bad = [int(x) for x in out.tolist()]
+    assert bad[0] == 0, f"{bad[0]} mismatches over {cs.numel()} constants; first (c,x) bits {bad[1]:#x}"
+
+
+@pytest.mark.parametrize("dt", ["f32", "bf16"])
+def test_fused_adamw_outside_the_packed_box_bit_exact(K, dt):
+    """Inputs that leave the packed path's box take the IEEE tail instead; both must equal the oracle:
+    zero and tiny parameters, zero / denormal / huge gradients and second moments, infinities, and
+    per-launch constants outside the box (eps = 0, eps = 1e-20, beta2 so close to 1 that sqrt(bc2) < 2^-10)."""
+    n = 8192 + 40
+    rng = np.random.default_rng(11)
+    tdt = TDT[dt]
+
+    def mk(vals):
+        return torch.tensor(vals, dtype=torch.float32).to(tdt).to(DEV)
+
+    special_p = [0.0, -0.0, 1e-38, -3e-35, 1e-30, 0.5, -2.0, 1e20, 3e38]
+    special_g = [0.0, 1e-40, -1e-38, 1e-25, 1e-12, 1e-3, -1.0, 1e4, 1e12, -3e19, 1e30, float("inf")]
+    p0 = rng.choice(special_p, n)
+    g0 = rng.choice(special_g, n)
+    v0 = np.abs(rng.choice(special_g[:-1], n)) * np.abs(rng.choice(special_g[:-1], n))
+    m0 = rng.choice(special_g[:-1], n) * 0.1
+    # some whole groups stay inside the box so both tails run in one launch
+    p0[:4096], g0[:4096] = rng.normal(0, 0.02, 4096), rng.normal(0, 0.01, 4096)
+    v0[:4096], m0[:4096] = rng.normal(0, 0.01, 4096) ** 2, rng.normal(0, 0.005, 4096)
+    for hp in (HP, dict(HP, eps=0.0), dict(HP, eps=1e-20), dict(HP, beta2=0.99999999), dict(HP, eps=1e-8, lr=10.0)):
+        with np.errstate(all="ignore"):
+            p, g, m, v = mk(p0), mk(g0), mk(m0), mk(np.float32(v0))
+        pn, gn, mn, vn = to_np(p), to_np(g), to_np(m), to_np(v)
+        for step, clip in ((1, None), (2, 0.5)):
+            coef = None if clip is None else torch.tensor([clip], dtype=torch.float32, device=DEV)
+            K.adamw(K.table([[p], [g], [m], [v]], [n]), tdt, tdt, tdt, step=step, clip_coef=coef,
+                    prefer_device=False, **hp)
+            with np.errstate(all="ignore"):
+                oracle.fused_clip_adamw(pn, gn, mn, vn, step=step, clip_coef=clip, **hp)
+            torch.cuda.synchronize()
+            for name, got, want in (("p", p, pn), ("m", m, mn), ("v", v, vn)):
+                a = to_np(got)
+                a = a.view(np.uint16 if a.dtype == np.uint16 else np.uint32)
+                b = want.view(np.uint16 if want.dtype == np.uint16 else np.uint32)
+                gf, wf = got.float().cpu().numpy(), (from_np(want).float().cpu().numpy())
+                same = (a == b) | (np.isnan(gf) & np.isnan(wf))          # NaN payloads are not part of the contract
+                assert same.all(), (dt, hp, step, name, int((~same).sum()), np.flatnonzero(~same)[:5])

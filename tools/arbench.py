@@ -57,13 +57,29 @@ def main():
     res["nccl+norm"] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws)
     ms = timed(lambda: dist.all_reduce(arena.tensor))
     res["nccl"] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws)
+    inv = float(torch.tensor(1.0 / ws, dtype=torch.float32))
+    sweep = os.environ.get("ARBENCH_SWEEP", "0") == "1"
     for mode in ("peer", "mc"):
         if mode == "mc" and not arena.multicast:
             continue
         arena.use_multicast = mode == "mc"
-        arena.tensor.normal_(0, 0.01)
-        ms = timed(lambda: K.allreduce_sumsq(tab, torch.bfloat16, arena, ss))
-        res[f"fused-{mode}"] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws)
+        wire = S * ((1 + 1 / ws) if mode == "mc" else 2 * (ws - 1) / ws)      # bytes per GPU and NVLink direction
+        configs = [(0, 0)]
+        if sweep:
+            configs += [(c, u) for c in (1, 2, 3) for u in ((0,) if mode == "peer" else (2, 4, 8))]
+        for ctas, unroll in configs:
+            os.environ["DDPB200_AR_CTAS"] = str(ctas)
+            os.environ["DDPB200_AR_UNROLL"] = str(unroll)
+            for scale in (1.0, inv):
+                arena.tensor.normal_(0, 0.01)
+                ms = timed(lambda: K.allreduce_sumsq(tab, torch.bfloat16, arena, ss, scale=scale))
+                key = f"fused-{mode}" + ("" if (ctas, unroll) == (0, 0) else f"-ctas{ctas}-unroll{unroll}") + ("" if scale == 1.0 else "-scaled")
+                res[key] = dict(ms=ms, algbw=S / ms / 1e6, busbw=S / ms / 1e6 * 2 * (ws - 1) / ws,
+                                wire_gbs_per_direction=wire / ms / 1e6, wire_frac_of_900=wire / ms / 1e6 / 900)
+                if rank == 0 and sweep:
+                    print(key, res[key], flush=True)
+        os.environ["DDPB200_AR_CTAS"] = "0"
+        os.environ["DDPB200_AR_UNROLL"] = "0"
     if rank == 0:
         print(json.dumps(res))
     dist.destroy_process_group()

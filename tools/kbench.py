@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--segments", default="llama")
     ap.add_argument("--only", default="")
     ap.add_argument("--sustained", type=int, default=0)
+    ap.add_argument("--chunk", type=int, default=0, help="chunk_elems of the AdamW table (0 = the library's suggestion)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     K = ddp_b200.CudaKernels()
@@ -73,7 +74,7 @@ def main():
         m = torch.zeros(n, dtype=dt, device=dev)
         v = torch.zeros(n, dtype=dt, device=dev)
         coef = torch.tensor([0.0028], dtype=torch.float32, device=dev)
-        tab = K.table([views(p), views(g), views(m), views(v)], numel, device=dev)
+        tab = K.table([views(p), views(g), views(m), views(v)], numel, chunk_elems=args.chunk or None, device=dev)
         hp = dict(lr=5e-5, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
         step = [0]
 
