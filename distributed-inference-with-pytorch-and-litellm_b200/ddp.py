@@ -102,6 +102,7 @@ class DistributedDataParallel(nn.Module):
         self.static_graph = static_graph
         self.gradient_as_bucket_view = gradient_as_bucket_view
         self.require_backward_grad_sync = True
+        self.require_forward_param_sync = True
         self.process_group = process_group if process_group is not None else dist.group.WORLD
         self.world_size = dist.get_world_size(self.process_group)
         self._inv_world_size = float(np.float32(1.0 / self.world_size))     # float(1.0/ws), as div_factor_
@@ -144,8 +145,14 @@ class DistributedDataParallel(nn.Module):
         self._use_side_stream = os.environ.get("PYTORCH_DDP_USE_SIDE_STREAM", "1") == "1"
         self._copy_stream = None
         # bucket allreduce + norm as ONE kernel over NVLink peer memory instead of NCCL + a norm pass
+        # fused_allreduce: True = required (raises if symmetric memory cannot be set up), False = NCCL,
+        # None = the environment's choice, DDPB200_FUSED_ALLREDUCE = 1 | 0 | auto (default auto: use it where it
+        # can be set up on every rank, otherwise say so once and use NCCL)
+        self._fused_optional = False
         if fused_allreduce is None:
-            fused_allreduce = os.environ.get("DDPB200_FUSED_ALLREDUCE", "0") == "1"
+            env = os.environ.get("DDPB200_FUSED_ALLREDUCE", "auto")
+            fused_allreduce = env in ("1", "auto")
+            self._fused_optional = env == "auto"
         self._fused = bool(fused_allreduce) and self._cuda and 1 < self.world_size <= 8
         self._sym = {}
         # sharded update (ZeRO-1 style, see zero.py): reduce-scatter instead of allreduce, parameters
@@ -285,8 +292,23 @@ class DistributedDataParallel(nn.Module):
         if self._fused:
             from .symm import SymmetricArena
             max_chunks = sum(p.numel() for p in self._params) // 2048 + len(self._params) + 1
-            self._sym = {dt: SymmetricArena(n, dt, self.device, self.process_group, max_chunks)
-                         for dt, n in sorted(arena_len.items(), key=lambda kv: str(kv[0]))}
+            err = None
+            try:
+                self._sym = {dt: SymmetricArena(n, dt, self.device, self.process_group, max_chunks)
+                             for dt, n in sorted(arena_len.items(), key=lambda kv: str(kv[0]))}
+            except Exception as e:          # no NVLink peer access / no symmetric-memory support on this box
+                if not self._fused_optional:
+                    raise
+                err = e
+            if self._fused_optional:        # every rank must take the same branch: agree
+                ok = torch.tensor([0 if err is not None else 1], device=self.device)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.process_group)
+                if int(ok) == 0:
+                    import warnings
+                    warnings.warn("ddp_b200: symmetric memory for the fused bucket allreduce could not be set up on every "
+                                  f"rank ({type(err).__name__ if err else 'another rank failed'}); using NCCL")
+                    self._fused, self._sym = False, {}
+        if self._fused:
             self._arenas = {dt: a.tensor for dt, a in self._sym.items()}
         else:
             self._arenas = {dt: torch.zeros(max(n, 1), dtype=dt, device=self.device) for dt, n in arena_len.items()}
@@ -309,6 +331,12 @@ class DistributedDataParallel(nn.Module):
                 # spread them over both, multicast does not: 7.33 vs 7.47 ms per step at 8 ranks
                 for a_ in list(self._sym.values()) + list(self._param_sym.values()):
                     a_.use_multicast = False
+            # tuning: the transport of each phase on its own (reduce-scatter of gradients / all-gather of parameters)
+            for env, arenas in (("DDPB200_ZERO_GRAD_MODE", self._sym), ("DDPB200_ZERO_PARAM_MODE", self._param_sym)):
+                want = os.environ.get(env)
+                if want in ("peer", "mc"):
+                    for a_ in arenas.values():
+                        a_.use_multicast = want == "mc" and bool(a_.multicast)
             with torch.no_grad():
                 for bk in self._buckets:            # same layout as the gradient arena: same byte offsets
                     pa = self._param_sym[bk.dtype].tensor
@@ -345,14 +373,20 @@ class DistributedDataParallel(nn.Module):
             self._prepare_for_backward()
         elif torch.is_grad_enabled():
             self._sumsq_valid = False        # no_sync(): gradients will change without being reduced or normed
-        if self.broadcast_buffers and self.world_size > 1 and self.require_backward_grad_sync:
-            bufs = [b for _, b in self.module.named_buffers()]
+        # _sync_buffers in _pre_forward (distributed.py:1553-1600): gated on require_forward_param_sync, which the
+        # PREVIOUS forward's _post_forward set — so the forward after a no_sync() / no-grad forward does not
+        # broadcast, exactly as in torch; buffers named in _ddp_params_and_buffers_to_ignore are left alone
+        if self.broadcast_buffers and self.world_size > 1 and self.require_forward_param_sync:
+            bufs = [b for n_, b in self.module.named_buffers() if n_ not in self.parameters_to_ignore]
             if bufs:
                 with torch.no_grad():
-                    self._broadcast_coalesced(bufs)     # _sync_buffers, distributed.py:1553-1600
+                    self._broadcast_coalesced(bufs)
         if self.device_ids is not None:
             inputs, kwargs = self._to_device(inputs), self._to_device(kwargs)   # _pre_forward, distributed.py:1602-1622
-        return self.module(*inputs, **kwargs)
+        out = self.module(*inputs, **kwargs)
+        # _post_forward (distributed.py:1624-1660)
+        self.require_forward_param_sync = bool(torch.is_grad_enabled() and self.require_backward_grad_sync)
+        return out
 
     def _to_device(self, obj):
         """Inputs to the module's device, as torch's DDP does when device_ids is given: host tensors are

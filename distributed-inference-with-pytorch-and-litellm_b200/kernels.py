@@ -272,6 +272,10 @@ class CudaKernels:
                 lr = float(lr)
         flags = (_lib.ADAMW_ROUND_CLIPPED_GRAD if round_clipped else 0) | (_lib.ADAMW_MAXIMIZE if maximize else 0)
         pm = param_arena.peer_map(0)
+        # the owners are about to overwrite every rank's parameters: no rank may still be reading them (a late
+        # backward op, an eval forward or an EMA on another stream of a slower rank). The reduce-scatter's
+        # barrier only proves the peers packed their gradients, so there is one here as well as after.
+        param_arena.barrier()
         rc = _lib.lib().ddpb200_sharded_adamw_allgather(
             ptr, n, chunks, tab.chunk_elems, dtype_code(dtype), grad_arena.tensor.data_ptr(), ctypes.addressof(pm),
             exp_avg_shard.data_ptr(), exp_avg_sq_shard.data_ptr(), float(lr), lr_ptr, beta1, beta2, eps, weight_decay,

@@ -346,3 +346,71 @@ def _worker_bf16_buckets(rank, ws, port):
 
 def test_bf16_gradient_buckets_for_fp32_model(native_lib):
     mp.spawn(_worker_bf16_buckets, args=(2, 29691), nprocs=2, join=True)
+
+
+def _worker_buffers(rank, ws, port):
+    """Buffers (BatchNorm running statistics) next to stock DDP through train / no_sync / eval forwards:
+    torch gates the buffer broadcast on require_forward_param_sync, which the PREVIOUS forward set
+    (TORCH/nn/parallel/distributed.py:1553-1660), and skips buffers named in
+    _ddp_params_and_buffers_to_ignore; ours must land its broadcasts on the same iterations."""
+    _setup(rank, ws, port)
+    import copy
+    import ddp_b200
+    from oracle_backend import OracleKernels
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.l1 = torch.nn.Linear(12, 16)
+            self.bn = torch.nn.BatchNorm1d(16)
+            self.l2 = torch.nn.Linear(16, 4)
+            self.register_buffer("private", torch.zeros(3))
+
+        def forward(self, x):
+            self.private += x.mean() * (1 + dist.get_rank())          # rank-dependent, ignored by DDP below
+            return self.l2(self.bn(torch.relu(self.l1(x))))
+
+    torch.manual_seed(0)
+    base = Net()
+    base._ddp_params_and_buffers_to_ignore = ["private"]
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ref = torch.nn.parallel.DistributedDataParallel(a)
+    ours = ddp_b200.DistributedDataParallel(b, kernels=OracleKernels())
+    assert ours.require_forward_param_sync == ref.require_forward_param_sync
+
+    def same_buffers(tag):
+        for (n1, x), (n2, y) in zip(a.named_buffers(), b.named_buffers()):
+            assert n1 == n2 and torch.equal(x, y), (tag, n1, rank)
+
+    g = torch.Generator().manual_seed(100 + rank)
+    plan = ["train", "nosync", "train", "eval", "train", "nosync", "nosync", "train"]
+    for it, kind in enumerate(plan):
+        x = torch.randn(8, 12, generator=g)
+        for model in (ref, ours):
+            if kind == "eval":
+                model.eval()
+                with torch.no_grad():
+                    model(x)
+                model.train()
+            elif kind == "nosync":
+                with model.no_sync():
+                    model(x).sum().backward()
+            else:
+                model(x).sum().backward()
+        assert ours.require_forward_param_sync == ref.require_forward_param_sync, (it, kind)
+        same_buffers((it, kind))
+        if kind == "train":
+            for p, q in zip(a.parameters(), b.parameters()):
+                assert torch.equal(p.grad, q.grad), (it, kind)
+                p.grad = None
+                q.grad = None
+    # the ignored buffer was never broadcast: it still differs between the ranks
+    mine = b.private.clone()
+    other = [torch.zeros_like(mine) for _ in range(ws)]
+    dist.all_gather(other, mine)
+    assert not torch.equal(other[0], other[1])
+    dist.destroy_process_group()
+
+
+def test_buffer_broadcast_follows_torch(native_lib):
+    mp.spawn(_worker_buffers, args=(2, 29671), nprocs=2, join=True)

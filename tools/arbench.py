@@ -80,6 +80,48 @@ def main():
                     print(key, res[key], flush=True)
         os.environ["DDPB200_AR_CTAS"] = "0"
         os.environ["DDPB200_AR_UNROLL"] = "0"
+    # NVLink bytes really moved by one collective, from the driver's per-link data counters on GPU `local`
+    # (nvidia-smi nvlink -gt d: KiB transmitted / received per link), around 20 back-to-back launches
+    if os.environ.get("ARBENCH_NVLINK", "0") == "1":
+        import re
+        import subprocess
+
+        def counters():
+            try:
+                txt = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(local)], stdout=subprocess.PIPE,
+                                     stderr=subprocess.STDOUT, text=True, timeout=30).stdout
+            except Exception as e:
+                return None, None, str(e)
+            tx = sum(int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", txt))
+            rx = sum(int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", txt))
+            return tx * 1024, rx * 1024, txt
+        reps = 20
+        for mode in ("peer", "mc"):
+            if mode == "mc" and not arena.multicast:
+                continue
+            arena.use_multicast = mode == "mc"
+            for what in ("fused", "nccl"):
+                if what == "nccl" and mode == "mc":
+                    continue
+                torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+                tx0, rx0, raw0 = counters()
+                for _ in range(reps):
+                    if what == "fused":
+                        K.allreduce_sumsq(tab, torch.bfloat16, arena, ss)
+                    else:
+                        dist.all_reduce(arena.tensor)
+                torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+                tx1, rx1, raw1 = counters()
+                if tx0 is None or tx1 is None or (tx1 == tx0 and rx1 == rx0):
+                    if rank == 0:
+                        res[f"nvlink-{what}-{mode}"] = {"error": "counters unavailable or not moving", "sample": (raw1 or "")[:300]}
+                    continue
+                key = f"nvlink-{what}-{mode}" if what == "fused" else "nvlink-nccl"
+                expect = S * ((1 + 1 / ws) if mode == "mc" else 2 * (ws - 1) / ws)
+                if rank == 0:
+                    res[key] = dict(tx_bytes_per_collective=(tx1 - tx0) / reps, rx_bytes_per_collective=(rx1 - rx0) / reps,
+                                    tx_over_S=(tx1 - tx0) / reps / S, rx_over_S=(rx1 - rx0) / reps / S,
+                                    model_bytes_per_direction=expect, model_over_S=expect / S, gpu=local)
     if rank == 0:
         print(json.dumps(res))
     dist.destroy_process_group()

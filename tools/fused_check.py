@@ -86,9 +86,10 @@ def main():
                 if mode == "peer" or (pow2 and not tiny):
                     assert torch.equal(arena.tensor, two_step), (mode, dt, ws, tiny, "folded scale differs from pack + sum")
                     assert torch.equal(ss, ss2), (mode, dt, ws, tiny, "sums of squares differ")
-                elif pow2:     # multicast, subnormal results: the scaled sum is rounded once more; off by <= 1 subnormal ulp
+                elif pow2:     # multicast, subnormal results: pack rounds every rank's scaled value to a subnormal, the
+                    # folded form rounds the scaled SUM; measured 4 subnormal steps apart at 2, 4 and 8 ranks
                     d = (arena.tensor.double() - two_step.double()).abs().max()
-                    lim = 2.0 ** -133 if dt == torch.bfloat16 else 2.0 ** -149
+                    lim = 8 * (2.0 ** -133 if dt == torch.bfloat16 else 2.0 ** -149)
                     assert float(d) <= lim, (mode, dt, ws, float(d))
                     assert torch.equal(arena.tensor[4096:], two_step[4096:])
         del arena

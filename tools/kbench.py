@@ -74,7 +74,7 @@ def main():
         m = torch.zeros(n, dtype=dt, device=dev)
         v = torch.zeros(n, dtype=dt, device=dev)
         coef = torch.tensor([0.0028], dtype=torch.float32, device=dev)
-        tab = K.table([views(p), views(g), views(m), views(v)], numel, chunk_elems=args.chunk or None, device=dev)
+        tab = K.table([views(p), views(g), views(m), views(v)], numel, chunk_elems=args.chunk or ddp_b200.optim.adamw_chunk_elems(n), device=dev)
         hp = dict(lr=5e-5, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
         step = [0]
 

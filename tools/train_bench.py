@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--seq", type=int, default=2048)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours,stock")     # also: ours-fused (fused peer-memory collective per bucket)
+    ap.add_argument("--impl", default="ours,stock")     # also: ours-fused / ours-nccl (force the bucket collective)
     args = ap.parse_args()
     rank, ws, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     dev = torch.device("cuda", local)
@@ -50,9 +50,10 @@ def main():
 
     for impl in args.impl.split(","):
         model = copy.deepcopy(base)
-        if impl in ("ours", "ours-fused"):
+        if impl in ("ours", "ours-fused", "ours-nccl"):
+            # ours = the library's default (fused peer-memory collective where it can be set up, else NCCL)
             ddp = ddp_b200.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
-                                                   fused_allreduce=(impl == "ours-fused"))
+                                                   fused_allreduce={"ours": None, "ours-fused": True, "ours-nccl": False}[impl])
             opt = ddp_b200.AdamW(model.parameters(), lr=5e-5)
             clip = lambda: ddp.clip_grad_norm_(1.0, fused_optimizer=opt)                   # noqa: E731
         else:
