@@ -14,6 +14,7 @@ from .ddp import DistributedDataParallel, GradBucket
 from .kernels import CudaKernels, SegTable, default_kernels
 from .optim import AdamW
 from .zero import ShardedAdamW
+from . import ops  # noqa: F401  (registers the torch.library ops of namespace ddp_b200)
 
 DDP = DistributedDataParallel
 

@@ -56,7 +56,7 @@ SIGNATURES = {
     "ddpb200_l2norm_finalize": (ctypes.c_int, [_vp, _i64, _i32, _f32, _vp, _vp]),
     "ddpb200_scale_by_device_scalar": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _vp, _vp]),
     "ddpb200_fused_clip_adamw": (ctypes.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _f64, _vp,
-                                                _f64, _f64, _f64, _f64, _i64, _vp, _vp, _vp, _u32, _vp]),
+                                                _f64, _f64, _f64, _f64, _i64, _vp, _vp, _vp, _vp, _u32, _vp]),
     "ddpb200_adamw_bias_corrections": (ctypes.c_int, [_f64, _f64, _i64, _vp]),
     "ddpb200_allreduce_sumsq_chunks": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _vp]),
     "ddpb200_fold_chunk_partials": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),

@@ -12,6 +12,7 @@ read+write sweep. In that mode ``p.grad`` is left unscaled — an opt-in deviati
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Iterable, List, Optional, Tuple, Union
 
 import torch
@@ -40,16 +41,25 @@ def clip_grad_norm_(parameters: Union[torch.Tensor, Iterable[torch.Tensor]], max
             raise RuntimeError("ddp_b200.clip_grad_norm_ needs contiguous gradients")
         groups.setdefault(g.dtype, []).append(g)
 
+    # default backend: through the registered torch.library ops (ops.py) — the same C-ABI calls, by name
+    use_ops = kernels is None and device.type == "cuda" and os.environ.get("DDPB200_USE_OPS", "1") == "1"
     sumsq = torch.empty(len(grads), dtype=torch.float32, device=device)
     tables: List[Tuple] = []
     pos = 0
     for dt, gl in groups.items():
-        tab = k.table([None, gl, None, None], [g.numel() for g in gl])
-        k.sumsq(tab, dt, sumsq[pos:pos + len(gl)], prefer_device=False)
-        tables.append((tab, dt))
+        if use_ops:
+            torch.ops.ddp_b200.l2norm_sumsq(gl, sumsq[pos:pos + len(gl)])
+            tables.append((gl, dt))
+        else:
+            tab = k.table([None, gl, None, None], [g.numel() for g in gl])
+            k.sumsq(tab, dt, sumsq[pos:pos + len(gl)], prefer_device=False)
+            tables.append((tab, dt))
         pos += len(gl)
     all_bf16 = all(dt == torch.bfloat16 for dt in groups)
-    out = k.norm_finalize(sumsq, float(max_norm), torch_bf16=(torch_rounding and all_bf16))
+    if use_ops:
+        out = torch.ops.ddp_b200.l2norm_finalize(sumsq, float(max_norm), bool(torch_rounding and all_bf16))
+    else:
+        out = k.norm_finalize(sumsq, float(max_norm), torch_bf16=(torch_rounding and all_bf16))
 
     if error_if_nonfinite and not bool(torch.isfinite(out[0])):
         raise RuntimeError(
@@ -62,5 +72,8 @@ def clip_grad_norm_(parameters: Union[torch.Tensor, Iterable[torch.Tensor]], max
         fused_optimizer.set_clip_coef(coef)
     else:
         for tab, dt in tables:
-            k.scale_by(tab, dt, coef, prefer_device=False)
+            if use_ops:
+                torch.ops.ddp_b200.scale_by_(tab, coef)
+            else:
+                k.scale_by(tab, dt, coef, prefer_device=False)
     return out[0].to(grads[0].dtype)

@@ -17,9 +17,15 @@
 //     (div_by_const, common.cuh) instead of the ~10-instruction IEEE division sequence.
 //   * 256-bit global accesses with L2 evict-first (sm_100a) halve the LSU instruction count.
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include "launch.cuh"
 #include "adamw_math.cuh"
+
+namespace ddpb200 {
+// default of the TMA-staged variant for all-bf16 fast modes on a device table: 0 stages = off (register kernel)
+constexpr int kBulkDefaultStages = 0, kBulkDefaultCtas = 2;
+}
 
 namespace ddpb200 {
 
@@ -65,9 +71,10 @@ __global__ void __launch_bounds__(kThreads, CT)
 adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems,
              AdamScalars a, const float* __restrict__ lr_ptr, const float* __restrict__ clip_ptr,
              const float* __restrict__ grad_scale_ptr, const float* __restrict__ found_inf_ptr,
-             uint32_t flags) {
+             const float* __restrict__ step_ptr, uint32_t flags) {
   constexpr bool any_f32 = (PDT == DDPB200_F32 || GDT == DDPB200_F32 || SDT == DDPB200_F32);
   if (found_inf_ptr && __ldg(found_inf_ptr) == 1.0f) return;      // GradScaler skip (cuh:137-139)
+  if (step_ptr) device_bias_corrections(a, __ldg(step_ptr));      // step count kept on the device (AMP: no host sync)
   const AdamRuntime r = make_adam_runtime(a, lr_ptr, clip_ptr, grad_scale_ptr, flags);
   const bool store_g = (flags & DDPB200_ADAMW_STORE_GRAD) != 0;
   const AdamPacked pk = make_adam_packed(a, r);
@@ -105,7 +112,7 @@ template <int PDT, int GDT, int SDT, int MODE>
 static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int64_t total_chunks,
                         int64_t chunk_elems, const AdamScalars& a, const float* lr_ptr,
                         const float* clip, const float* grad_scale, const float* found_inf,
-                        uint32_t flags, cudaStream_t st) {
+                        const float* step_ptr, uint32_t flags, cudaStream_t st) {
   return for_each_table_slice(table, table_loc == DDPB200_TABLE_DEVICE, n, total_chunks,
     [&](auto& tab, int64_t chunks, int64_t, int64_t) -> int {
       using Tab = std::remove_reference_t<decltype(tab)>;
@@ -123,7 +130,10 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
       constexpr bool narrow = !any_f32 && MODE != kModeGeneral;
       constexpr int CT = narrow ? 4 : 2;
       constexpr int MAXVEC = narrow ? 16 : 32;
-      const int64_t cap = (int64_t)sms * CT;
+      // tuning: DDPB200_ADAMW_CTAS = CTAs per SM actually launched (<= CT; fractional: 3.5 = half the SMs hold 4
+      // CTAs, half 3), read at every launch so that tools/kbench.py can sweep it in one process
+      const double env_ct = [] { const char* e = getenv("DDPB200_ADAMW_CTAS"); return e ? atof(e) : 0.0; }();
+      const int64_t cap = (env_ct > 0.0 && env_ct <= CT) ? (int64_t)(sms * env_ct) : (int64_t)sms * CT;
       const int grid = (int)(chunks < cap ? chunks : cap);
       if (grid == 0) return 0;
       // A/B switch for tools/kbench.py only: DDPB200_ADAMW_WIDE=1 selects 256-bit x 3 CTAs/SM
@@ -132,7 +142,7 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
         if (wide) {
           const int64_t wcap = (int64_t)sms * 3;
           adamw_kernel<Tab, PDT, GDT, SDT, MODE, 3, 32><<<(int)(chunks < wcap ? chunks : wcap), kThreads, 0, st>>>(
-              tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
+              tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, step_ptr, flags);
           return (int)cudaGetLastError();
         }
       }
@@ -142,16 +152,24 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
       if constexpr (narrow) {
         if (scalar_math) {
           adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT, MAXVEC, false><<<grid, kThreads, 0, st>>>(
-              tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
+              tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, step_ptr, flags);
           return (int)cudaGetLastError();
         }
       }
       adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT, MAXVEC><<<grid, kThreads, 0, st>>>(
-          tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, flags);
+          tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, step_ptr, flags);
       return (int)cudaGetLastError();
     });
 }
 
+}  // namespace ddpb200
+
+namespace ddpb200 {
+// adamw_bulk.cu
+template <int MODE>
+int launch_adamw_bulk(const ddpb200_seg* table, int table_loc, int64_t n, int64_t total_chunks, int64_t chunk_elems,
+                      const AdamScalars& a, const float* lr_ptr, const float* clip, uint32_t flags, cudaStream_t st,
+                      int stages, int ctas, int* rc);
 }  // namespace ddpb200
 
 using namespace ddpb200;
@@ -172,11 +190,12 @@ extern "C" DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, in
                                         int32_t param_dtype, int32_t grad_dtype,
                                         int32_t state_dtype, double lr, const float* lr_ptr,
                                         double beta1, double beta2, double eps,
-                                        double weight_decay, int64_t step, const float* clip_coef,
-                                        const float* grad_scale, const float* found_inf,
+                                        double weight_decay, int64_t step, const float* step_ptr,
+                                        const float* clip_coef, const float* grad_scale, const float* found_inf,
                                         uint32_t flags, void* stream) {
-  if (!valid_chunking(n, total_chunks, chunk_elems) || (n > 0 && !table) || step < 1)
+  if (!valid_chunking(n, total_chunks, chunk_elems) || (n > 0 && !table) || (step < 1 && !step_ptr))
     return DDPB200_E_INVALID;
+  if (step < 1) step = 1;          // step_ptr given: the device value is used, this only seeds the host-side scalars
   if (n == 0) return 0;
   float bc[2];
   ddpb200_adamw_bias_corrections(beta1, beta2, step, bc);
@@ -188,16 +207,32 @@ extern "C" DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, in
                      !(flags & (DDPB200_ADAMW_MAXIMIZE | DDPB200_ADAMW_STORE_GRAD));
   if (plain && clip_coef && (flags & DDPB200_ADAMW_ROUND_CLIPPED_GRAD)) mode = kModeFastClip;
   else if (plain && !clip_coef) mode = kModeFastPlain;
+  // DDPB200_ADAMW_BULK="stages,ctas" takes the all-bf16 fast modes on a device table through the TMA-staged
+  // variant (adamw_bulk.cu); "0" switches it off; read at every launch so that tools/kbench.py can sweep it
+  if (mode != kModeGeneral && param_dtype == DDPB200_BF16 && grad_dtype == DDPB200_BF16 && state_dtype == DDPB200_BF16 &&
+      !found_inf && !step_ptr) {
+    int stages = kBulkDefaultStages, ctas = kBulkDefaultCtas;
+    if (const char* e = getenv("DDPB200_ADAMW_BULK")) {
+      if (sscanf(e, "%d,%d", &stages, &ctas) != 2) stages = 0;
+    }
+    if (stages > 0) {
+      int rc = 0;
+      const int took = mode == kModeFastClip
+          ? launch_adamw_bulk<kModeFastClip>(table, table_loc, n, total_chunks, chunk_elems, a, lr_ptr, clip_coef, flags, st, stages, ctas, &rc)
+          : launch_adamw_bulk<kModeFastPlain>(table, table_loc, n, total_chunks, chunk_elems, a, lr_ptr, clip_coef, flags, st, stages, ctas, &rc);
+      if (took) return rc;
+    }
+  }
 #define DDPB200_ADAMW_CASE(P, G, S)                                                                   \
   if (param_dtype == P && grad_dtype == G && state_dtype == S) {                                      \
     if (mode == kModeFastClip)                                                                        \
       return launch_adamw<P, G, S, kModeFastClip>(table, table_loc, n, total_chunks, chunk_elems, a,  \
-                                                  lr_ptr, clip_coef, grad_scale, found_inf, flags, st); \
+                                                  lr_ptr, clip_coef, grad_scale, found_inf, step_ptr, flags, st); \
     if (mode == kModeFastPlain)                                                                       \
       return launch_adamw<P, G, S, kModeFastPlain>(table, table_loc, n, total_chunks, chunk_elems, a, \
-                                                   lr_ptr, clip_coef, grad_scale, found_inf, flags, st); \
+                                                   lr_ptr, clip_coef, grad_scale, found_inf, step_ptr, flags, st); \
     return launch_adamw<P, G, S, kModeGeneral>(table, table_loc, n, total_chunks, chunk_elems, a,     \
-                                               lr_ptr, clip_coef, grad_scale, found_inf, flags, st);  \
+                                               lr_ptr, clip_coef, grad_scale, found_inf, step_ptr, flags, st);  \
   }
   DDPB200_ADAMW_CASE(DDPB200_F32, DDPB200_F32, DDPB200_F32)
   DDPB200_ADAMW_CASE(DDPB200_BF16, DDPB200_BF16, DDPB200_BF16)

@@ -251,6 +251,10 @@ extern "C" DDPB200_API int ddpb200_l2norm_sumsq_static(const ddpb200_seg* table,
                                                        int64_t chunk_elems, int32_t dtype,
                                                        float* sumsq_out, void* stream) {
   if (total_chunks > DDPB200_STATIC_SCRATCH_MAX_CHUNKS) return DDPB200_E_TOO_LARGE;
+  // every argument is checked before anything is enqueued: a refused call leaves the shared array alone
+  if (!valid_chunking(n, total_chunks, chunk_elems) || (n > 0 && (!table || !sumsq_out))) return DDPB200_E_INVALID;
+  if (dtype != DDPB200_F32 && dtype != DDPB200_BF16) return DDPB200_E_UNSUPPORTED;
+  if (n == 0) return 0;
   void* base = nullptr;
   const int rc = static_scratch_for_current_device(&base);
   if (rc != 0) return rc;

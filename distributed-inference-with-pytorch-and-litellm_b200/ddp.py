@@ -473,13 +473,22 @@ class DistributedDataParallel(nn.Module):
         limits = bucketing.rebuild_bucket_limits(self.bucket_bytes_cap, self.bucket_bytes_cap_default)
         idx, lim = bucketing.compute_bucket_assignment_by_size([self._params[i] for i in order], limits,
                                                                None, order)
-        if self.gradient_as_bucket_view:
-            for p in self._params:          # grads alias the old buckets: detach before freeing them
-                if p.grad is not None:
-                    p.grad = p.grad.clone()
         if self._cuda:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
+        # gradients that alias the old buckets move straight into their new views, bucket by bucket: the old
+        # arena stays alive only through these references (peak = old + new arena, no third copy of every gradient)
+        old_grads = [p.grad for p in self._params] if self.gradient_as_bucket_view else None
         self._build_buckets(idx, lim)
+        if old_grads is not None:
+            with torch.no_grad():
+                for bk in self._buckets:
+                    for pi, view in zip(bk.spec.indices, bk.views):
+                        g = old_grads[pi]
+                        if g is not None and g.dtype == view.dtype:
+                            view.copy_(g)
+                            self._params[pi].grad = view
+                            old_grads[pi] = None
+            del old_grads
         self._has_rebuilt = True
         self._ready_order = []
         self._stats["rebuilt_bucket_sizes"] = [bk.buffer.numel() * bk.buffer.element_size() for bk in self._buckets]

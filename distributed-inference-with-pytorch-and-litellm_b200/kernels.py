@@ -116,6 +116,25 @@ class _Workspace:
         return ent
 
 
+class _NoRange:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NO_RANGE = _NoRange()
+
+
+def _op_range(name: str):
+    """While a torch profiler is active, bracket a kernel launch with a range named like the registered op
+    (ops.py), so that the scheduler's direct C-ABI calls show up under the same names; free otherwise."""
+    if torch.autograd.profiler._is_profiler_enabled:
+        return torch.profiler.record_function(name)
+    return _NO_RANGE
+
+
 class CudaKernels:
     """The product kernel backend. Every method enqueues on torch's CURRENT stream and returns
     without synchronising."""
@@ -160,15 +179,16 @@ class CudaKernels:
         With sumsq_out (fp32, one slot per row of the slice) also the sum of squares of dst."""
         ptr, loc, n, chunks = tab.args(first, count, prefer_device)
         st = self._stream()
-        if sumsq_out is not None:
-            self._require_cuda(sumsq_out)
-            partials, ticket = self._ws.get(sumsq_out.device, st, chunks)
-            rc = _lib.lib().ddpb200_pack_scale_cast(ptr, loc, n, chunks, tab.chunk_elems, dtype_code(src_dtype),
-                                                    dtype_code(dst_dtype), scale, sumsq_out.data_ptr(),
-                                                    partials.data_ptr(), ticket.data_ptr(), st)
-        else:
-            rc = _lib.lib().ddpb200_pack_scale_cast(ptr, loc, n, chunks, tab.chunk_elems, dtype_code(src_dtype),
-                                                    dtype_code(dst_dtype), scale, None, None, None, st)
+        with _op_range("ddp_b200::pack_scale_cast"):
+            if sumsq_out is not None:
+                self._require_cuda(sumsq_out)
+                partials, ticket = self._ws.get(sumsq_out.device, st, chunks)
+                rc = _lib.lib().ddpb200_pack_scale_cast(ptr, loc, n, chunks, tab.chunk_elems, dtype_code(src_dtype),
+                                                        dtype_code(dst_dtype), scale, sumsq_out.data_ptr(),
+                                                        partials.data_ptr(), ticket.data_ptr(), st)
+            else:
+                rc = _lib.lib().ddpb200_pack_scale_cast(ptr, loc, n, chunks, tab.chunk_elems, dtype_code(src_dtype),
+                                                        dtype_code(dst_dtype), scale, None, None, None, st)
         _lib.check(rc, "ddpb200_pack_scale_cast")
 
     # ---- kernel (b) ---------------------------------------------------------------------------
@@ -179,8 +199,9 @@ class CudaKernels:
         ptr, loc, n, chunks = tab.args(first, count, prefer_device)
         st = self._stream()
         partials, ticket = self._ws.get(out.device, st, chunks)
-        rc = _lib.lib().ddpb200_l2norm_sumsq(ptr, loc, n, chunks, tab.chunk_elems, dtype_code(dtype),
-                                             out.data_ptr(), partials.data_ptr(), ticket.data_ptr(), st)
+        with _op_range("ddp_b200::l2norm_sumsq"):
+            rc = _lib.lib().ddpb200_l2norm_sumsq(ptr, loc, n, chunks, tab.chunk_elems, dtype_code(dtype),
+                                                 out.data_ptr(), partials.data_ptr(), ticket.data_ptr(), st)
         _lib.check(rc, "ddpb200_l2norm_sumsq")
 
     def norm_finalize(self, sumsq: torch.Tensor, max_norm: float, torch_bf16: bool,
@@ -210,8 +231,9 @@ class CudaKernels:
               weight_decay: float, step: int, clip_coef: Optional[torch.Tensor] = None,
               grad_scale: Optional[torch.Tensor] = None, found_inf: Optional[torch.Tensor] = None,
               round_clipped: bool = True, store_grad: bool = False, maximize: bool = False,
-              prefer_device: bool = True) -> None:
-        """One fused unscale+clip+AdamW pass over all rows: ptr = [param, grad, exp_avg, exp_avg_sq]."""
+              prefer_device: bool = True, step_tensor: Optional[torch.Tensor] = None) -> None:
+        """One fused unscale+clip+AdamW pass over all rows: ptr = [param, grad, exp_avg, exp_avg_sq].
+        step_tensor (device fp32 scalar) replaces the host-side `step` for the bias corrections."""
         ptr, loc, n, chunks = tab.args(0, None, prefer_device)
         lr_ptr = None
         if isinstance(lr, torch.Tensor):
@@ -221,12 +243,14 @@ class CudaKernels:
                 lr = float(lr)
         flags = ((_lib.ADAMW_ROUND_CLIPPED_GRAD if round_clipped else 0) |
                  (_lib.ADAMW_STORE_GRAD if store_grad else 0) | (_lib.ADAMW_MAXIMIZE if maximize else 0))
-        rc = _lib.lib().ddpb200_fused_clip_adamw(
-            ptr, loc, n, chunks, tab.chunk_elems, dtype_code(param_dtype), dtype_code(grad_dtype),
-            dtype_code(state_dtype), float(lr), lr_ptr, beta1, beta2, eps, weight_decay, int(step),
-            None if clip_coef is None else clip_coef.data_ptr(),
-            None if grad_scale is None else grad_scale.data_ptr(),
-            None if found_inf is None else found_inf.data_ptr(), flags, self._stream())
+        with _op_range("ddp_b200::fused_clip_adamw_"):
+            rc = _lib.lib().ddpb200_fused_clip_adamw(
+                ptr, loc, n, chunks, tab.chunk_elems, dtype_code(param_dtype), dtype_code(grad_dtype),
+                dtype_code(state_dtype), float(lr), lr_ptr, beta1, beta2, eps, weight_decay, int(step),
+                None if step_tensor is None else step_tensor.data_ptr(),
+                None if clip_coef is None else clip_coef.data_ptr(),
+                None if grad_scale is None else grad_scale.data_ptr(),
+                None if found_inf is None else found_inf.data_ptr(), flags, self._stream())
         _lib.check(rc, "ddpb200_fused_clip_adamw")
 
 
@@ -245,14 +269,15 @@ class CudaKernels:
         chunk_off = int(tab.chunk_begins[first])
         st = self._stream()
         L = _lib.lib()
-        arena.barrier()                                   # every rank has packed this range
-        pm = arena.peer_map(chunk_off)
-        fn = L.ddpb200_reduce_scatter_sumsq_chunks if scatter else L.ddpb200_allreduce_sumsq_chunks
-        _lib.check(fn(ptr, n, chunks, tab.chunk_elems, dtype_code(dtype), ctypes.addressof(pm),
-                      int(arena.use_multicast), float(scale), st), "ddpb200_allreduce_sumsq_chunks")
-        arena.barrier()                                   # every rank has written its chunks everywhere
-        _lib.check(L.ddpb200_fold_chunk_partials(ptr, n, chunks, arena.partials.data_ptr() + 4 * chunk_off,
-                                                 sumsq_out.data_ptr(), st), "ddpb200_fold_chunk_partials")
+        with _op_range("ddp_b200::allreduce_sumsq_"):
+            arena.barrier()                                   # every rank has packed this range
+            pm = arena.peer_map(chunk_off)
+            fn = L.ddpb200_reduce_scatter_sumsq_chunks if scatter else L.ddpb200_allreduce_sumsq_chunks
+            _lib.check(fn(ptr, n, chunks, tab.chunk_elems, dtype_code(dtype), ctypes.addressof(pm),
+                          int(arena.use_multicast), float(scale), st), "ddpb200_allreduce_sumsq_chunks")
+            arena.barrier()                                   # every rank has written its chunks everywhere
+            _lib.check(L.ddpb200_fold_chunk_partials(ptr, n, chunks, arena.partials.data_ptr() + 4 * chunk_off,
+                                                     sumsq_out.data_ptr(), st), "ddpb200_fold_chunk_partials")
 
 
     def sharded_adamw(self, tab: SegTable, dtype: torch.dtype, grad_arena, param_arena, exp_avg_shard: torch.Tensor,

@@ -12,6 +12,7 @@ read+write sweep over all gradients.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Tuple
 
 import numpy as np
@@ -61,8 +62,11 @@ class AdamW(Optimizer):
                         differentiable=differentiable, fused=fused, decoupled_weight_decay=True)
         super().__init__(params, defaults)
         self._kernels = kernels
+        # default backend on CUDA: go through the registered torch.library op (DDPB200_USE_OPS=0: straight to ctypes)
+        self._use_ops = kernels is None and os.environ.get("DDPB200_USE_OPS", "1") == "1"
         self._state_dtype = state_dtype
         self._clip_coef: Optional[torch.Tensor] = None
+        self._dev_steps_live = False
         self._tables: Dict[Tuple, Tuple[np.ndarray, np.ndarray, SegTable]] = {}
         self._plan: Dict[int, dict] = {}
         self.round_clipped_grad = True   # reproduce torch's rounding of g*coef to the grad dtype
@@ -98,8 +102,14 @@ class AdamW(Optimizer):
         self._clip_coef = None
         grad_scale = getattr(self, "grad_scale", None)
         found_inf = getattr(self, "found_inf", None)
-        if found_inf is not None and float(found_inf) == 1.0:
-            return loss  # GradScaler: skip the step, counters untouched (adam.py:869-876)
+        # GradScaler: whether this step happens is only known on the device. No host sync (torch's fused path
+        # has none either, adam.py:869-876): the kernel reads found_inf and does nothing if it is set, and the
+        # step count used for the bias corrections lives on the device for as long as a scaler drives us.
+        amp = found_inf is not None and found_inf.is_cuda
+        if found_inf is not None and not amp and float(found_inf) == 1.0:
+            return loss
+        if not amp and self._dev_steps_live:
+            self._sync_steps()
         k = self._k()
         self.launches_last_step = 0
 
@@ -110,14 +120,38 @@ class AdamW(Optimizer):
                 continue
             for li, launch in enumerate(self._partition(gi, with_grad)):
                 key, plist, steps = launch[0], launch[1], launch[2]
+                device, pdt, gdt, sdt = key
+                if amp:
+                    if launch[6] is None:
+                        launch[6] = torch.full((1,), float(launch[3]), dtype=torch.float32, device=device)
+                        self._dev_steps_live = True
+                    dev_step = launch[6]
+                    dev_step.add_(1.0)                # state_steps += 1 ... (adam.py fused path)
+                    tab = self._table_for((gi, li) + key, plist, device)
+                    k.adamw(tab, pdt, gdt, sdt, lr=group["lr"], beta1=beta1, beta2=beta2, eps=group["eps"],
+                            weight_decay=group["weight_decay"], step=max(1, launch[3]), clip_coef=clip_coef,
+                            grad_scale=grad_scale, found_inf=found_inf, round_clipped=self.round_clipped_grad,
+                            store_grad=grad_scale is not None, maximize=group["maximize"], step_tensor=dev_step)
+                    dev_step.sub_(found_inf.to(torch.float32).reshape(1))   # ... -= found_inf: a skipped step does not count
+                    self.launches_last_step += 1
+                    continue
                 torch._foreach_add_(steps, 1.0)       # the per-parameter `step` scalars (CPU), one call
                 launch[3] += 1
-                device, pdt, gdt, sdt = key
-                tab = self._table_for((gi, li) + key, plist, device)
-                k.adamw(tab, pdt, gdt, sdt, lr=group["lr"], beta1=beta1, beta2=beta2, eps=group["eps"],
-                        weight_decay=group["weight_decay"], step=launch[3], clip_coef=clip_coef,
-                        grad_scale=grad_scale, found_inf=None, round_clipped=self.round_clipped_grad,
-                        store_grad=grad_scale is not None, maximize=group["maximize"])
+                if self._use_ops and device.type == "cuda":
+                    # through the dispatcher: torch.ops.ddp_b200.fused_clip_adamw_ (ops.py), the registered form
+                    # of the same C-ABI call — visible to torch.profiler / torch.compile by name
+                    lr = group["lr"]
+                    lr_t = lr if isinstance(lr, torch.Tensor) and lr.is_cuda else None
+                    torch.ops.ddp_b200.fused_clip_adamw_(
+                        plist, [p.grad for p in plist], launch[4], launch[5], 0.0 if lr_t is not None else float(lr),
+                        beta1, beta2, group["weight_decay"], group["eps"], launch[3], group["maximize"],
+                        self.round_clipped_grad, grad_scale is not None, clip_coef, grad_scale, None, lr_t)
+                else:
+                    tab = self._table_for((gi, li) + key, plist, device)
+                    k.adamw(tab, pdt, gdt, sdt, lr=group["lr"], beta1=beta1, beta2=beta2, eps=group["eps"],
+                            weight_decay=group["weight_decay"], step=launch[3], clip_coef=clip_coef,
+                            grad_scale=grad_scale, found_inf=None, round_clipped=self.round_clipped_grad,
+                            store_grad=grad_scale is not None, maximize=group["maximize"])
                 self.launches_last_step += 1
         return loss
 
@@ -128,6 +162,8 @@ class AdamW(Optimizer):
         ordinary training step) it is reused without touching per-parameter state again."""
         ids = [id(p) for p in with_grad]
         ent = self._plan.get(gi)
+        if ent is not None and ent[0] != ids and self._dev_steps_live:
+            self._sync_steps()              # the split changes: bring the CPU step scalars up to date first
         if ent is not None and ent[0] == ids and all(L[1][0].grad.dtype == L[0][2] for L in ent[1]):
             return ent[1]
         groups: Dict[Tuple, List[torch.Tensor]] = {}
@@ -138,9 +174,30 @@ class AdamW(Optimizer):
                 raise RuntimeError("ddp_b200.AdamW needs contiguous parameters and gradients")
             st = self._init_state(p)
             groups.setdefault((p.device, p.dtype, p.grad.dtype, st["exp_avg"].dtype, int(st["step"])), []).append(p)
-        launches = [[k5[:4], plist, [self.state[p]["step"] for p in plist], k5[4]] for k5, plist in groups.items()]
+        launches = [[k5[:4], plist, [self.state[p]["step"] for p in plist], k5[4],
+                     [self.state[p]["exp_avg"] for p in plist], [self.state[p]["exp_avg_sq"] for p in plist], None]
+                    for k5, plist in groups.items()]
         self._plan[gi] = (ids, launches)
         return launches
+
+    def _sync_steps(self) -> None:
+        """Device-resident step counts (GradScaler flow) back into the per-parameter CPU `step` scalars that
+        `state_dict()` exposes. One device-to-host read per launch group; called at checkpoints and when the
+        scaler stops driving the optimizer, never inside a scaled step."""
+        for ent in self._plan.values():
+            for launch in ent[1]:
+                if launch[6] is not None:
+                    v = float(launch[6])
+                    launch[3] = int(v)
+                    for st in launch[2]:
+                        st.fill_(v)
+                    launch[6] = None
+        self._dev_steps_live = False
+
+    def state_dict(self):
+        if self._dev_steps_live:
+            self._sync_steps()
+        return super().state_dict()
 
     def load_state_dict(self, state_dict) -> None:
         super().load_state_dict(state_dict)

@@ -20,15 +20,24 @@ from __future__ import annotations
 from typing import Optional
 
 import torch
+from torch.optim.optimizer import Optimizer
 
 
-class ShardedAdamW:
+class ShardedAdamW(Optimizer):
+    """A ``torch.optim.Optimizer`` (LR schedulers, ``param_groups``, ``zero_grad``, ``isinstance`` checks all
+    work) whose per-parameter state is NOT in ``self.state``: each rank holds its 1/world of ``exp_avg`` /
+    ``exp_avg_sq`` as two flat shards laid out by chunk. One parameter group (the update is one launch over
+    the whole arena). ``GradScaler`` is not supported: after a reduce-scatter a rank only sees the averaged
+    gradients of the chunks it owns, so an inf check would need its own collective; bf16 training, which
+    this path is for, does not scale."""
+
     def __init__(self, ddp, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, *, maximize: bool = False):
         if not getattr(ddp, "_zero", False):
             raise RuntimeError("ShardedAdamW needs DistributedDataParallel(..., fused_allreduce=True, shard_optimizer=True)")
+        if not 0.0 <= lr or not 0.0 <= eps or not 0.0 <= weight_decay or not (0.0 <= betas[0] < 1.0 and 0.0 <= betas[1] < 1.0):
+            raise ValueError("ShardedAdamW: invalid hyper-parameter")
         self.ddp = ddp
-        self.defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, maximize=maximize)
-        self.param_groups = [dict(self.defaults, params=list(ddp._params))]
+        super().__init__(list(ddp._params), dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, maximize=maximize))
         self.step_count = 0
         self._clip_coef: Optional[torch.Tensor] = None
         self.round_clipped_grad = True
@@ -40,15 +49,13 @@ class ShardedAdamW:
         self.exp_avg = torch.zeros(slots * tab.chunk_elems, dtype=dt, device=ddp.device)
         self.exp_avg_sq = torch.zeros(slots * tab.chunk_elems, dtype=dt, device=ddp.device)
 
+    def add_param_group(self, param_group) -> None:
+        if getattr(self, "param_groups", None):
+            raise NotImplementedError("ShardedAdamW updates the whole bucket arena in one launch: one parameter group")
+        super().add_param_group(param_group)
+
     def set_clip_coef(self, coef: Optional[torch.Tensor]) -> None:
         self._clip_coef = coef
-
-    def zero_grad(self, set_to_none: bool = True) -> None:
-        for p in self.ddp._params:
-            if set_to_none:
-                p.grad = None
-            elif p.grad is not None:
-                p.grad.zero_()
 
     @torch.no_grad()
     def step(self, closure=None, *, clip_coef: Optional[torch.Tensor] = None):
@@ -112,8 +119,48 @@ class ShardedAdamW:
         return {"state": {i: state[i] for i in sorted(state)}, "param_groups": [g]}
 
     def load_state_dict(self, sd: dict) -> None:
-        if not sd.get("sharded") or sd["world_size"] != self.ddp.world_size or sd["rank"] != self.ddp.rank:
-            raise ValueError("ShardedAdamW.load_state_dict: shard of another rank / world size")
-        self.step_count = int(sd["step"])
-        self.exp_avg.copy_(sd["exp_avg_shard"])
-        self.exp_avg_sq.copy_(sd["exp_avg_sq_shard"])
+        """Either this rank's own ``state_dict()``, or a state dict in ``torch.optim.AdamW``'s format — what
+        ``consolidated_state_dict()`` returns and what ``torch.optim.AdamW`` / ``ddp_b200.AdamW`` save: per
+        parameter (DDP registration order) ``step`` / ``exp_avg`` / ``exp_avg_sq``. From the latter every rank
+        keeps the chunks it owns (chunk a of the table lives on rank a % world at slot a // world); all
+        parameters must share one step count (one launch, one bias correction)."""
+        ddp = self.ddp
+        if sd.get("sharded"):
+            if sd["world_size"] != ddp.world_size or sd["rank"] != ddp.rank:
+                raise ValueError("ShardedAdamW.load_state_dict: shard of another rank / world size")
+            if sd["chunk_elems"] != ddp._view_table.chunk_elems:
+                raise ValueError("ShardedAdamW.load_state_dict: saved with another chunk size")
+            self.step_count = int(sd["step"])
+            self.exp_avg.copy_(sd["exp_avg_shard"])
+            self.exp_avg_sq.copy_(sd["exp_avg_sq_shard"])
+            for k, v in sd["param_groups"][0].items():
+                self.param_groups[0][k] = v
+            return
+        state, groups = sd["state"], sd["param_groups"]
+        if len(groups) != 1 or len(groups[0]["params"]) != len(ddp._params):
+            raise ValueError("ShardedAdamW.load_state_dict: expected one parameter group over all DDP parameters")
+        ws, rank, tab = ddp.world_size, ddp.rank, ddp._view_table
+        ce = tab.chunk_elems
+        steps = {int(float(state[k]["step"])) for k in state}
+        if len(steps) > 1:
+            raise ValueError(f"ShardedAdamW.load_state_dict: parameters at different step counts {sorted(steps)}")
+        self.exp_avg.zero_()
+        self.exp_avg_sq.zero_()
+        ids = groups[0]["params"]
+        for row, pi in enumerate(ddp._order):
+            ent = state.get(ids[pi], state.get(str(ids[pi])))
+            if ent is None:
+                continue                    # a parameter that never stepped: zeros
+            n = ddp._params[pi].numel()
+            first_chunk = int(tab.chunk_begins[row])
+            for name, shard in (("exp_avg", self.exp_avg), ("exp_avg_sq", self.exp_avg_sq)):
+                src = ent[name].reshape(-1).to(device=shard.device, dtype=shard.dtype)
+                for k in range(int(tab.chunk_begins[row + 1]) - first_chunk):
+                    a = first_chunk + k
+                    if a % ws == rank:
+                        ln = min(ce, n - k * ce)
+                        shard[(a // ws) * ce:(a // ws) * ce + ln] = src[k * ce:k * ce + ln]
+        self.step_count = steps.pop() if steps else 0
+        for k, v in groups[0].items():
+            if k != "params" and k in self.param_groups[0]:
+                self.param_groups[0][k] = v

@@ -242,14 +242,17 @@ DDPB200_API int ddpb200_sharded_adamw_allgather(
  *   p -= (lr*wd)*p;  m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g
  *   p -= (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps),  bc = 1 - beta^step (step >= 1)
  * lr_ptr (device, optional) overrides lr. found_inf (device, optional): if *found_inf==1
- * the launch is a no-op. clip_coef / grad_scale are device pointers so that no host sync
+ * the launch is a no-op. step_ptr (device fp32 scalar, optional) overrides step: the bias corrections are
+ * then taken on the device from *step_ptr (same formula), which is how the GradScaler flow runs without a
+ * host sync — the caller adds 1 to it before the launch and subtracts *found_inf after, as
+ * TORCH/optim/adam.py's fused path does with its device-resident state_steps. clip_coef / grad_scale are device pointers so that no host sync
  * sits between the norm and the update. */
 DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, int32_t table_loc, int64_t n, int64_t total_chunks,
                              int64_t chunk_elems, int32_t param_dtype, int32_t grad_dtype,
                              int32_t state_dtype, double lr, const float* lr_ptr,
                              double beta1, double beta2, double eps, double weight_decay,
-                             int64_t step, const float* clip_coef, const float* grad_scale,
-                             const float* found_inf, uint32_t flags, void* stream);
+                             int64_t step, const float* step_ptr, const float* clip_coef,
+                             const float* grad_scale, const float* found_inf, uint32_t flags, void* stream);
 
 /* The two fp32 scalars the kernel derives from `step`: out[0] = 1 - b1^step,
  * out[1] = sqrt(1 - b2^step), with b = beta rounded to fp32 (as the recurrences use it), the

@@ -58,7 +58,7 @@ class OracleKernels:
 
     def adamw(self, tab, param_dtype, grad_dtype, state_dtype, *, lr, beta1, beta2, eps, weight_decay, step,
               clip_coef=None, grad_scale=None, found_inf=None, round_clipped=True, store_grad=False,
-              maximize=False, prefer_device=True):
+              maximize=False, prefer_device=True, step_tensor=None):
         self.calls["adamw"] += 1
         L = oracle.lib()
         flags = (1 if round_clipped else 0) | (2 if store_grad else 0) | (4 if maximize else 0)

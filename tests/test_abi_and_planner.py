@@ -127,9 +127,9 @@ def test_bias_corrections_match_oracle(native_lib):
 def test_invalid_arguments_are_rejected_without_a_gpu(native_lib):
     # argument validation happens before any CUDA call, so these are safe on a CPU-only box
     assert native_lib.ddpb200_fused_clip_adamw(None, 0, 3, 3, 2048, 0, 0, 0, 1e-3, None, 0.9, 0.999, 1e-8, 0.01, 1,
-                                               None, None, None, 0, None) == -1
+                                               None, None, None, None, 0, None) == -1
     assert native_lib.ddpb200_fused_clip_adamw(None, 0, 0, 0, 1000, 0, 0, 0, 1e-3, None, 0.9, 0.999, 1e-8, 0.01, 1,
-                                               None, None, None, 0, None) == -1   # chunk not a multiple of 2048
+                                               None, None, None, None, 0, None) == -1   # chunk not a multiple of 2048
     assert native_lib.ddpb200_l2norm_finalize(None, 5, 0, 1.0, None, None) == -1
     assert native_lib.ddpb200_pack_scale_cast(None, 0, 0, 0, 2048, 7, 0, 1.0, None, None, None, None) == -2  # dtype 7
 

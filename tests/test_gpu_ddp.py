@@ -244,6 +244,19 @@ def _sharded_vs_replicated(rank, ws, mode):
             assert torch.equal(st["exp_avg"], rep_state[i]["exp_avg"]), (mode, dtype, i)
             assert torch.equal(st["exp_avg_sq"], rep_state[i]["exp_avg_sq"]), (mode, dtype, i)
         torch.optim.AdamW(list(b.parameters()), lr=1e-2).load_state_dict(full)
+        # it is a torch Optimizer: LR schedulers drive it, and it loads torch-format state (its own
+        # consolidated form, or the replicated optimizer's state_dict) back into the shards
+        assert isinstance(o_shd, torch.optim.Optimizer)
+        sched = torch.optim.lr_scheduler.StepLR(o_shd, step_size=1, gamma=0.5)
+        sched.step()
+        assert o_shd.param_groups[0]["lr"] == 5e-3
+        for src in (full, o_rep.state_dict()):
+            fresh = ddp_b200.ShardedAdamW(shd, lr=1e-2)
+            fresh.load_state_dict(src)
+            assert fresh.step_count == 5
+            assert torch.equal(fresh.exp_avg, o_shd.exp_avg) and torch.equal(fresh.exp_avg_sq, o_shd.exp_avg_sq), (mode, dtype)
+        fresh.load_state_dict(o_shd.state_dict())
+        assert torch.equal(fresh.exp_avg, o_shd.exp_avg) and fresh.param_groups[0]["lr"] == 5e-3
 
 
 def _fused_vs_nccl(rank, ws, mode):

@@ -76,3 +76,26 @@ def test_static_scratch_rejects_sizes_beyond_its_limit():
                                                   torch.cuda.current_stream().cuda_stream) == 0
     torch.cuda.synchronize()
     assert float(out) == 0.0
+
+
+def test_static_scratch_exactly_at_its_limit():
+    """total_chunks == the limit is accepted and uses the last float of the array: ones through 262,144
+    chunks of 2048 elements (the last one half full) sum to their count exactly, and the caller-scratch
+    entry point agrees bit for bit; invalid arguments are refused before anything is enqueued."""
+    dev = torch.device("cuda", 0)
+    limit = _lib.STATIC_SCRATCH_MAX_CHUNKS
+    n = limit * 2048 - 1024                             # ragged last chunk, still exactly `limit` chunks; n fits fp32
+    ones = torch.ones(n, dtype=torch.bfloat16, device=dev)
+    got, want, tab = _both([ones], torch.bfloat16, chunk_elems=2048)
+    assert tab.total_chunks == limit
+    assert torch.equal(got, want) and float(got) == float(n)
+    ptr, loc, cnt, chunks = tab.args(0, None, prefer_device=False)
+    st = torch.cuda.current_stream().cuda_stream
+    L = _lib.lib()
+    assert L.ddpb200_l2norm_sumsq_static(ptr, loc, cnt, -1, 2048, _lib.BF16, got.data_ptr(), st) == -1
+    assert L.ddpb200_l2norm_sumsq_static(ptr, loc, cnt, chunks, 1000, _lib.BF16, got.data_ptr(), st) == -1
+    assert L.ddpb200_l2norm_sumsq_static(ptr, loc, cnt, chunks, 2048, 7, got.data_ptr(), st) == -2
+    assert L.ddpb200_l2norm_sumsq_static(ptr, loc, cnt, chunks, 2048, _lib.BF16, None, st) == -1
+    # and the array still works afterwards
+    got2, want2, _ = _both([ones[:70001]], torch.bfloat16, chunk_elems=2048)
+    assert torch.equal(got2, want2) and float(got2) == 70001.0

@@ -39,6 +39,8 @@ def main():
     ap.add_argument("--segments", default="llama")
     ap.add_argument("--only", default="")
     ap.add_argument("--sustained", type=int, default=0)
+    ap.add_argument("--alloc", default="flat", choices=["flat", "separate"],
+                    help="p/g/m/v as slices of four flat buffers, or every tensor its own allocation (as a model has them)")
     ap.add_argument("--chunk", type=int, default=0, help="chunk_elems of the AdamW table (0 = the library's suggestion)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
@@ -74,7 +76,15 @@ def main():
         m = torch.zeros(n, dtype=dt, device=dev)
         v = torch.zeros(n, dtype=dt, device=dev)
         coef = torch.tensor([0.0028], dtype=torch.float32, device=dev)
-        tab = K.table([views(p), views(g), views(m), views(v)], numel, chunk_elems=args.chunk or ddp_b200.optim.adamw_chunk_elems(n), device=dev)
+        if args.alloc == "separate":
+            pv, gv = [x.clone() for x in views(p)], [x.clone() for x in views(g)]
+            mv, vv = [], []
+            for x in pv:                # interleaved, like a lazily initialised optimizer allocates its state
+                mv.append(torch.zeros_like(x))
+                vv.append(torch.zeros_like(x))
+        else:
+            pv, gv, mv, vv = views(p), views(g), views(m), views(v)
+        tab = K.table([pv, gv, mv, vv], numel, chunk_elems=args.chunk or ddp_b200.optim.adamw_chunk_elems(n), device=dev)
         hp = dict(lr=5e-5, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
         step = [0]
 
