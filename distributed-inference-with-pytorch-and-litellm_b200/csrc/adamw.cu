@@ -23,8 +23,11 @@
 #include "adamw_math.cuh"
 
 namespace ddpb200 {
-// default of the TMA-staged variant for all-bf16 fast modes on a device table: 0 stages = off (register kernel)
-constexpr int kBulkDefaultStages = 0, kBulkDefaultCtas = 2;
+// Default of the TMA-staged variant (adamw_bulk.cu) for all-bf16 fast modes on a device table: 2 stages x 2 CTAs/SM
+// = 64 KB in flight per SM. Llama-3.2-1B set, burst (10 launches) / 300 launches back to back, same box
+// (profiles/r02_adamw_kbench.txt): 2.68 / 2.72 ms against 2.82 / 2.78 for the register kernel; more in flight
+// loses (3 x 2: 2.87 / 2.85; 4 x 1 wins the burst, 2.63, and loses under the power cap, 2.89). 0 stages = off.
+constexpr int kBulkDefaultStages = 2, kBulkDefaultCtas = 2;
 }
 
 namespace ddpb200 {
