@@ -873,9 +873,16 @@ def _stock_cpu_worker(r, n, store, cfg, steps, warmup, threads, budget_s, out_pa
         opt.zero_grad()
 
     t0 = time.perf_counter()
+    warmed = 0
     for _ in range(warmup):
         one()
-    per = torch.tensor([(time.perf_counter() - t0) / max(1, warmup)], dtype=torch.float64)
+        warmed += 1
+        # bounded runs (many ranks on few cores): stop warming up once it has cost 20 s; every rank decides alike
+        slow = torch.tensor([1.0 if (budget_s is not None and time.perf_counter() - t0 > 20.0) else 0.0])
+        dist.all_reduce(slow, op=dist.ReduceOp.MAX)
+        if float(slow) > 0:
+            break
+    per = torch.tensor([(time.perf_counter() - t0) / max(1, warmed)], dtype=torch.float64)
     dist.all_reduce(per, op=dist.ReduceOp.MAX)
     # the whole run has to end within minutes: with more ranks than the host has cores to give them, a step
     # takes many seconds, and the step count is capped (every rank computes the same cap)
@@ -887,7 +894,8 @@ def _stock_cpu_worker(r, n, store, cfg, steps, warmup, threads, budget_s, out_pa
     dist.barrier()
     dt = time.perf_counter() - t0
     if r == 0:
-        json.dump({"rate": run / dt, "steps": run, "total": total, "threads": threads, "warmup_s_per_step": float(per)},
+        json.dump({"rate": run / dt, "steps": run, "total": total, "threads": threads, "warmup_s_per_step": float(per),
+                   "warmup": warmed},
                   open(out_path, "w"))
     dist.destroy_process_group()
 
@@ -978,9 +986,9 @@ def run_reference(args):
                             budget_s=None if ranks == 1 else 150.0)
     value = r["rate"] * ranks
     sample = (f"stock torch DDP(gloo, {ranks} rank{'s' if ranks > 1 else ''})+clip_grad_norm_+AdamW(default) on CPU, bf16, "
-              f"the full parameter set ({r['total']} elements per rank), {r['steps']} steps after {max(1, args.warmup)} warm-up, "
+              f"the full parameter set ({r['total']} elements per rank), {r['steps']} steps after {r['warmup']} warm-up, "
               f"{r['threads']} threads per rank")
-    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"], "warmup": max(1, args.warmup),
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"], "warmup": r["warmup"],
            "ms_per_step": 1e3 / r["rate"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "bf16", "data": "synthetic", "impl": "reference",
            "config": {"workload": reference_workload_string(args.workload, len(shapes), total_full),
