@@ -983,7 +983,7 @@ def run_reference(args):
     for k in [k for k in os.environ if k.startswith("TORCHELASTIC")]:
         os.environ.pop(k)
     r = stock_cpu_step_rate(cfg, steps=max(1, args.steps), warmup=max(1, args.warmup), ranks=ranks,
-                            budget_s=None if ranks == 1 else 150.0)
+                            budget_s=None if ranks == 1 else 175.0)
     value = r["rate"] * ranks
     sample = (f"stock torch DDP(gloo, {ranks} rank{'s' if ranks > 1 else ''})+clip_grad_norm_+AdamW(default) on CPU, bf16, "
               f"the full parameter set ({r['total']} elements per rank), {r['steps']} steps after {r['warmup']} warm-up, "

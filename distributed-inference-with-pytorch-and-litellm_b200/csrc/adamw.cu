@@ -151,8 +151,11 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
       }
       // A/B switch for tools/kbench.py only: DDPB200_ADAMW_PACKED=0 selects the scalar element arithmetic
       // (IEEE intrinsics per element) that round 1 shipped, for the all-bf16 fast modes
-      static const bool scalar_math = [] { const char* e = getenv("DDPB200_ADAMW_PACKED"); return e && atoi(e) == 0; }();
-      if constexpr (narrow) {
+      static const int packed_env = [] { const char* e = getenv("DDPB200_ADAMW_PACKED"); return e ? atoi(e) : -1; }();
+      // fp32 streams: the packed path's 119 registers cost more than its issue slots save (5.46 ms against 5.29 for
+      // the scalar arithmetic on the Llama-1B set, profiles/r02_kbench_all.txt), so it is the default only for all-bf16
+      const bool scalar_math = packed_env == 0 || (packed_env < 0 && !narrow);
+      if constexpr (MODE != kModeGeneral) {
         if (scalar_math) {
           adamw_kernel<Tab, PDT, GDT, SDT, MODE, CT, MAXVEC, false><<<grid, kThreads, 0, st>>>(
               tab, chunks, chunk_elems, a, lr_ptr, clip, grad_scale, found_inf, step_ptr, flags);
@@ -169,7 +172,7 @@ static int launch_adamw(const ddpb200_seg* table, int table_loc, int64_t n, int6
 
 namespace ddpb200 {
 // adamw_bulk.cu
-template <int MODE>
+template <int DT, int MODE>
 int launch_adamw_bulk(const ddpb200_seg* table, int table_loc, int64_t n, int64_t total_chunks, int64_t chunk_elems,
                       const AdamScalars& a, const float* lr_ptr, const float* clip, uint32_t flags, cudaStream_t st,
                       int stages, int ctas, int* rc);
@@ -210,19 +213,22 @@ extern "C" DDPB200_API int ddpb200_fused_clip_adamw(const ddpb200_seg* table, in
                      !(flags & (DDPB200_ADAMW_MAXIMIZE | DDPB200_ADAMW_STORE_GRAD));
   if (plain && clip_coef && (flags & DDPB200_ADAMW_ROUND_CLIPPED_GRAD)) mode = kModeFastClip;
   else if (plain && !clip_coef) mode = kModeFastPlain;
-  // DDPB200_ADAMW_BULK="stages,ctas" takes the all-bf16 fast modes on a device table through the TMA-staged
+  // DDPB200_ADAMW_BULK="stages,ctas" takes the all-bf16 / all-fp32 fast modes on a device table through the TMA-staged
   // variant (adamw_bulk.cu); "0" switches it off; read at every launch so that tools/kbench.py can sweep it
-  if (mode != kModeGeneral && param_dtype == DDPB200_BF16 && grad_dtype == DDPB200_BF16 && state_dtype == DDPB200_BF16 &&
-      !found_inf && !step_ptr) {
-    int stages = kBulkDefaultStages, ctas = kBulkDefaultCtas;
+  if (mode != kModeGeneral && param_dtype == grad_dtype && grad_dtype == state_dtype && !found_inf && !step_ptr) {
+    // all-fp32 stays on the register kernel by default: 5.19 / 5.25 ms (burst / sustained) against 5.32 / 5.34 staged
+    int stages = param_dtype == DDPB200_BF16 ? kBulkDefaultStages : 0, ctas = kBulkDefaultCtas;
     if (const char* e = getenv("DDPB200_ADAMW_BULK")) {
       if (sscanf(e, "%d,%d", &stages, &ctas) != 2) stages = 0;
     }
     if (stages > 0) {
-      int rc = 0;
-      const int took = mode == kModeFastClip
-          ? launch_adamw_bulk<kModeFastClip>(table, table_loc, n, total_chunks, chunk_elems, a, lr_ptr, clip_coef, flags, st, stages, ctas, &rc)
-          : launch_adamw_bulk<kModeFastPlain>(table, table_loc, n, total_chunks, chunk_elems, a, lr_ptr, clip_coef, flags, st, stages, ctas, &rc);
+      int rc = 0, took = 0;
+#define DDPB200_BULK_CALL(DT, MD) launch_adamw_bulk<DT, MD>(table, table_loc, n, total_chunks, chunk_elems, a, lr_ptr, clip_coef, flags, st, stages, ctas, &rc)
+      if (param_dtype == DDPB200_BF16)
+        took = mode == kModeFastClip ? DDPB200_BULK_CALL(DDPB200_BF16, kModeFastClip) : DDPB200_BULK_CALL(DDPB200_BF16, kModeFastPlain);
+      else
+        took = mode == kModeFastClip ? DDPB200_BULK_CALL(DDPB200_F32, kModeFastClip) : DDPB200_BULK_CALL(DDPB200_F32, kModeFastPlain);
+#undef DDPB200_BULK_CALL
       if (took) return rc;
     }
   }

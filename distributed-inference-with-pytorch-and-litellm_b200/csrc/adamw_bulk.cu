@@ -9,8 +9,8 @@
 // per CTA keeps NSTAGE tiles (NSTAGE x 16 KB) in flight whatever the eight consumer warps are doing; loads
 // cost no LSU issue slots and no registers; stores still go straight from registers (STG.128).
 //
-// All-bf16, fast modes only (the arithmetic is adamw_group_packed of adamw_math.cuh, bit-identical to
-// adamw.cu); a chunk whose four pointers are not 16-byte aligned, and the last < 8 elements of a segment, are
+// All-bf16 or all-fp32, fast modes only (16 bytes of every stream per thread and tile; the arithmetic is
+// adamw_group_packed of adamw_math.cuh, bit-identical to adamw.cu); a chunk whose four pointers are not 16-byte aligned, and the ragged last elements of a segment, are
 // read from global memory by the consumers as in adamw.cu. Selected at run time (see launch_adamw_bulk).
 #include <stdlib.h>
 #include "launch.cuh"
@@ -18,8 +18,8 @@
 
 namespace ddpb200 {
 
-constexpr int kBulkTile = 2048;                       // elements per tile and stream: 256 consumers x 8
-constexpr int kBulkConsumers = kThreads;              // 8 consumer warps
+constexpr int kBulkConsumers = kThreads;              // 8 consumer warps, 16 bytes of each stream per thread and tile
+constexpr int kBulkStreamBytes = kBulkConsumers * 16; // one stream's tile: 4 KB = 2048 bf16 / 1024 fp32 elements
 constexpr int kBulkThreads = kThreads + 32;           // + 1 producer warp (one lane works)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -49,14 +49,19 @@ __device__ __forceinline__ Raw<4> lds128(uint32_t addr) {
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x.r[0]), "=r"(x.r[1]), "=r"(x.r[2]), "=r"(x.r[3]) : "r"(addr));
   return x;
 }
-__device__ __forceinline__ void unpack_bf16x8(const Raw<4>& t, float (&v)[8]) {
+template <int DT> __device__ __forceinline__ void unpack16(const Raw<4>& t, float (&v)[16 / ElemOf<DT>::size]) {
+  if constexpr (DT == DDPB200_F32) {
 #pragma unroll
-  for (int k = 0; k < 4; ++k) { v[2 * k] = bf16_bits_to_f32(t.r[k] & 0xffffu); v[2 * k + 1] = __uint_as_float(t.r[k] & 0xffff0000u); }
+    for (int k = 0; k < 4; ++k) v[k] = __uint_as_float(t.r[k]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { v[2 * k] = bf16_bits_to_f32(t.r[k] & 0xffffu); v[2 * k + 1] = __uint_as_float(t.r[k] & 0xffff0000u); }
+  }
 }
 
 struct BulkChunk { char *P, *G, *M, *V; int64_t len; bool staged; };
 
-template <class Tab>
+template <int ES, class Tab>
 __device__ __forceinline__ BulkChunk bulk_chunk(const Tab& tab, int64_t c, int64_t chunk_base, int64_t total_chunks,
                                                 int64_t chunk_elems, SegCursor& cur) {
   const int s = find_seg_cached(tab, c + chunk_base, chunk_base + total_chunks, cur);
@@ -64,21 +69,23 @@ __device__ __forceinline__ BulkChunk bulk_chunk(const Tab& tab, int64_t c, int64
   const int64_t rest = tab.numel(s) - start;
   BulkChunk k;
   k.len = rest < chunk_elems ? rest : chunk_elems;
-  k.P = static_cast<char*>(tab.ptr(s, 0)) + start * 2;
-  k.G = static_cast<char*>(tab.ptr(s, 1)) + start * 2;
-  k.M = static_cast<char*>(tab.ptr(s, 2)) + start * 2;
-  k.V = static_cast<char*>(tab.ptr(s, 3)) + start * 2;
+  k.P = static_cast<char*>(tab.ptr(s, 0)) + start * ES;
+  k.G = static_cast<char*>(tab.ptr(s, 1)) + start * ES;
+  k.M = static_cast<char*>(tab.ptr(s, 2)) + start * ES;
+  k.V = static_cast<char*>(tab.ptr(s, 3)) + start * ES;
   k.staged = ((reinterpret_cast<uintptr_t>(k.P) | reinterpret_cast<uintptr_t>(k.G) | reinterpret_cast<uintptr_t>(k.M) |
                reinterpret_cast<uintptr_t>(k.V)) & 15) == 0;
   return k;
 }
 
-template <class Tab, int MODE, int NSTAGE, int CT>
+template <class Tab, int DT, int MODE, int NSTAGE, int CT>
 __global__ void __launch_bounds__(kBulkThreads, CT)
 adamw_bulk_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chunk_elems, AdamScalars a,
                   const float* __restrict__ lr_ptr, const float* __restrict__ clip_ptr, uint32_t flags) {
-  constexpr int DT = DDPB200_BF16;
-  constexpr uint32_t kStreamBytes = kBulkTile * 2;                  // one stream's tile
+  constexpr int ES = ElemOf<DT>::size;
+  constexpr int G = 16 / ES;                                        // elements per thread and tile
+  constexpr int kBulkTile = kBulkConsumers * G;                     // elements per tile and stream
+  constexpr uint32_t kStreamBytes = kBulkStreamBytes;
   constexpr uint32_t kStageBytes = 4 * kStreamBytes;
   extern __shared__ __align__(128) unsigned char smem[];
   const uint32_t data = smem_u32(smem);
@@ -99,18 +106,18 @@ adamw_bulk_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t
     // ---- producer: one lane walks the same tile sequence as the consumers, NSTAGE tiles ahead -------------
     if (lane != 0) return;
     for (int64_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
-      const BulkChunk k = bulk_chunk(tab, c, chunk_base, total_chunks, chunk_elems, cur);
+      const BulkChunk k = bulk_chunk<ES>(tab, c, chunk_base, total_chunks, chunk_elems, cur);
       for (int64_t t0 = 0; t0 < k.len; t0 += kBulkTile) {
         const int64_t cnt = (k.len - t0) < kBulkTile ? (k.len - t0) : kBulkTile;
-        const uint32_t bytes = k.staged ? (uint32_t)(cnt / 8 * 8) * 2 : 0u;
+        const uint32_t bytes = k.staged ? (uint32_t)(cnt / G * G) * ES : 0u;
         mbar_wait(empty + 8 * stage, phase ^ 1);                    // the consumers are done with this slot
         const uint32_t bar = full + 8 * stage, dst = data + stage * kStageBytes;
         if (bytes) {
           mbar_arrive_expect_tx(bar, 4 * bytes);
-          bulk_g2s(dst, k.G + t0 * 2, bytes, bar);
-          bulk_g2s(dst + kStreamBytes, k.P + t0 * 2, bytes, bar);
-          bulk_g2s(dst + 2 * kStreamBytes, k.M + t0 * 2, bytes, bar);
-          bulk_g2s(dst + 3 * kStreamBytes, k.V + t0 * 2, bytes, bar);
+          bulk_g2s(dst, k.G + t0 * ES, bytes, bar);
+          bulk_g2s(dst + kStreamBytes, k.P + t0 * ES, bytes, bar);
+          bulk_g2s(dst + 2 * kStreamBytes, k.M + t0 * ES, bytes, bar);
+          bulk_g2s(dst + 3 * kStreamBytes, k.V + t0 * ES, bytes, bar);
         } else {
           mbar_arrive(bar);                                         // nothing staged: the consumers read global memory
         }
@@ -124,29 +131,29 @@ adamw_bulk_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t
   const AdamRuntime r = make_adam_runtime(a, lr_ptr, clip_ptr, nullptr, flags);
   const AdamPacked pk = make_adam_packed(a, r);
   for (int64_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
-    const BulkChunk k = bulk_chunk(tab, c, chunk_base, total_chunks, chunk_elems, cur);
+    const BulkChunk k = bulk_chunk<ES>(tab, c, chunk_base, total_chunks, chunk_elems, cur);
     for (int64_t t0 = 0; t0 < k.len; t0 += kBulkTile) {
       const int64_t cnt = (k.len - t0) < kBulkTile ? (k.len - t0) : kBulkTile;
-      const int64_t vec = k.staged ? cnt / 8 * 8 : 0;
+      const int64_t vec = k.staged ? cnt / G * G : 0;
       mbar_wait(full + 8 * stage, phase);                           // the tile has landed
-      const int64_t i = (int64_t)threadIdx.x * 8;
-      float p[8], g[8], m[8], v[8];
+      const int64_t i = (int64_t)threadIdx.x * G;
+      float p[G], g[G], m[G], v[G];
       const bool mine = i < vec;
       if (mine) {
         const uint32_t src = data + stage * kStageBytes + threadIdx.x * 16;
-        unpack_bf16x8(lds128(src), g);
-        unpack_bf16x8(lds128(src + kStreamBytes), p);
-        unpack_bf16x8(lds128(src + 2 * kStreamBytes), m);
-        unpack_bf16x8(lds128(src + 3 * kStreamBytes), v);
+        unpack16<DT>(lds128(src), g);
+        unpack16<DT>(lds128(src + kStreamBytes), p);
+        unpack16<DT>(lds128(src + 2 * kStreamBytes), m);
+        unpack16<DT>(lds128(src + 3 * kStreamBytes), v);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty + 8 * stage);                // values are in registers: hand the slot back
       if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
       if (mine) {
-        adamw_group_packed<DT, MODE, 8>(p, g, m, v, a, r, pk);
-        GroupIO<DT, 8>::store(k.P, t0 + i, p);
-        GroupIO<DT, 8>::store(k.M, t0 + i, m);
-        GroupIO<DT, 8>::store(k.V, t0 + i, v);
+        adamw_group_packed<DT, MODE, G>(p, g, m, v, a, r, pk);
+        GroupIO<DT, G>::store(k.P, t0 + i, p);
+        GroupIO<DT, G>::store(k.M, t0 + i, m);
+        GroupIO<DT, G>::store(k.V, t0 + i, v);
       }
       // the ragged end of a segment, or a chunk that could not be staged: element by element from global memory
       for (int64_t j = t0 + vec + threadIdx.x; j < t0 + cnt; j += kBulkConsumers) {
@@ -161,7 +168,7 @@ adamw_bulk_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t
 }
 
 // 0 = not applicable (the caller falls through to the register kernel), else launched (or failed): *rc holds the code
-template <int MODE>
+template <int DT, int MODE>
 int launch_adamw_bulk(const ddpb200_seg* table, int table_loc, int64_t n, int64_t total_chunks, int64_t chunk_elems,
                       const AdamScalars& a, const float* lr_ptr, const float* clip, uint32_t flags, cudaStream_t st,
                       int stages, int ctas, int* rc) {
@@ -175,8 +182,8 @@ int launch_adamw_bulk(const ddpb200_seg* table, int table_loc, int64_t n, int64_
   if (grid == 0) { *rc = 0; return 1; }
 #define DDPB200_BULK_LAUNCH(NS, CTV)                                                                       \
   {                                                                                                       \
-    auto kern = adamw_bulk_kernel<DevTable, MODE, NS, CTV>;                                               \
-    const int smem = NS * 4 * kBulkTile * 2 + 2 * NS * 8;                                                 \
+    auto kern = adamw_bulk_kernel<DevTable, DT, MODE, NS, CTV>;                                           \
+    const int smem = NS * 4 * kBulkStreamBytes + 2 * NS * 8;                                              \
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);        \
     if (e != cudaSuccess) { *rc = (int)e; return 1; }                                                     \
     kern<<<grid, kBulkThreads, smem, st>>>(tab, total_chunks, chunk_elems, a, lr_ptr, clip, flags);        \
@@ -195,9 +202,13 @@ int launch_adamw_bulk(const ddpb200_seg* table, int table_loc, int64_t n, int64_
   return 0;
 }
 
-template int launch_adamw_bulk<kModeFastClip>(const ddpb200_seg*, int, int64_t, int64_t, int64_t, const AdamScalars&,
-                                              const float*, const float*, uint32_t, cudaStream_t, int, int, int*);
-template int launch_adamw_bulk<kModeFastPlain>(const ddpb200_seg*, int, int64_t, int64_t, int64_t, const AdamScalars&,
-                                               const float*, const float*, uint32_t, cudaStream_t, int, int, int*);
+#define DDPB200_BULK_INST(DT, MODE)                                                                                  \
+  template int launch_adamw_bulk<DT, MODE>(const ddpb200_seg*, int, int64_t, int64_t, int64_t, const AdamScalars&,   \
+                                           const float*, const float*, uint32_t, cudaStream_t, int, int, int*);
+DDPB200_BULK_INST(DDPB200_BF16, kModeFastClip)
+DDPB200_BULK_INST(DDPB200_BF16, kModeFastPlain)
+DDPB200_BULK_INST(DDPB200_F32, kModeFastClip)
+DDPB200_BULK_INST(DDPB200_F32, kModeFastPlain)
+#undef DDPB200_BULK_INST
 
 }  // namespace ddpb200

@@ -25,9 +25,10 @@ for line in out.splitlines():
 demangled = subprocess.run(["c++filt"], input="\n".join(funcs), stdout=subprocess.PIPE, text=True).stdout.splitlines()
 names = dict(zip(funcs, demangled))
 WANT = [  # (label, regex on the demangled name)
-    ("fused clip+AdamW, bf16, FastClip, TMA-staged 2 stages x 2 CTAs/SM (default, device table)", r"adamw_bulk_kernel<ddpb200::DevTable, 1, 2, 2>"),
+    ("fused clip+AdamW, bf16, FastClip, TMA-staged 2 stages x 2 CTAs/SM (default, device table)", r"adamw_bulk_kernel<ddpb200::DevTable, 1, 1, 2, 2>"),
     ("fused clip+AdamW, bf16, FastClip, register kernel 128-bit x 4 CTAs/SM, packed math (host tables)", r"adamw_kernel<ddpb200::DevTable, 1, 1, 1, 1, 4, 16, true>"),
-    ("fused clip+AdamW, fp32, FastClip, register kernel 256-bit x 2 CTAs/SM, packed math", r"adamw_kernel<ddpb200::DevTable, 0, 0, 0, 1, 2, 32, true>"),
+    ("fused clip+AdamW, fp32, FastClip, TMA-staged 2 stages x 2 CTAs/SM (default, device table)", r"adamw_bulk_kernel<ddpb200::DevTable, 0, 1, 2, 2>"),
+    ("fused clip+AdamW, fp32, FastClip, register kernel 256-bit x 2 CTAs/SM, scalar IEEE arithmetic (host tables)", r"adamw_kernel<ddpb200::DevTable, 0, 0, 0, 1, 2, 32, false>"),
     ("pack bf16 -> bf16 (+scale)", r"stream_kernel<ddpb200::DevTable, 1, 1, 0, 1, true, false, false>"),
     ("L2 norm bf16 (sum of squares)", r"stream_kernel<ddpb200::DevTable, 1, 1, 1, 1, false, true, false>"),
     ("fused allreduce+norm, bf16, multicast (multimem), unroll 4", r"fused_allreduce_kernel<1, 1, 2, false, 4>"),
