@@ -745,7 +745,8 @@ def run_ours(args):
             "fused_allreduces": stats1.get("fused_allreduces", 0) - stats0.get("fused_allreduces", 0),
             "allreduce_impl": ("fused peer-memory kernel (" + ("multicast" if any(a.use_multicast for a in ddp._sym.values()) else "peer") + ")")
                               if ddp._fused else ((fused_note or "nccl") if ws > 1 else "none"),
-            "roofline": {"kernel": "adamw_kernel (fused clip+AdamW, bf16)", "bound": "hbm", "achieved": achieved,
+            "roofline": {"kernel": ("sharded_adamw_kernel (AdamW on the owned chunks + parameter all-gather, bf16)" if zero1 else
+                                    "adamw_bulk_kernel (fused clip+AdamW, bf16, TMA-staged inputs)"), "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                          "frac_of_8000_nominal": achieved / 8000.0, "algorithmic_bytes_per_launch": alg_bytes,
                          "avg_launch_ms": adamw_ms, "traffic": adamw_traffic_from_profile()},
