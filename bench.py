@@ -2,19 +2,22 @@
 """bench.py — the DDP gradient-sync + clip + AdamW hot path on B200.
 
 A *step* is one pass of the hot path over one set of synthetic gradients for the Llama-3.2-1B
-architecture in bf16 (BASELINE.json configs[1]: 146 parameter tensors, 1,235,814,400 elements):
-N>1: per bucket pack (flatten + 1/world_size + cast) -> NCCL allreduce on a side stream ->
-per-tensor sum of squares; N=1: nothing to exchange, so one coalesced sum-of-squares launch over the
-gradients where they lie. Then total norm + clip coefficient on the device; then ONE fused
-clip+AdamW launch over all parameters. Forward/backward of the model are not part of the path
-(SURVEY.md §8f-2 lists them as the next row).
+architecture in bf16 (BASELINE.json configs[1]: 146 parameter tensors, 1,235,814,400 elements).
+N=1: nothing to exchange, so one coalesced sum-of-squares launch over the gradients where they lie, the total
+norm + clip coefficient on the device, ONE fused clip+AdamW launch over all parameters. N>1: the gradients live
+in the bucket arena (gradient_as_bucket_view), so a step is the fused allreduce+norm kernel over NVLink peer
+memory / NVSwitch multicast with the 1/world_size scale folded in (or NCCL + a norm launch), finalize, AdamW;
+--separate-grads adds the pack pass. Before the timed loop an N>1 run checks its collective against NCCL, across
+ranks and against the sharded update (`parity_check`; a failure is exit code 3). Forward/backward of the model
+are not part of the path (the next row) — the N=1 line carries them as the `train` side record,
+and torch's own CUDA kernels on the same tensors as `incumbent`.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--zero1] [--workload W]
 
 N>1 is launched by torchrun (one rank per GPU, NCCL). Prints ONE JSON line on rank 0.
 --impl reference times the reference's own CPU implementation of the same path: the UNMODIFIED
 stock torch code (DistributedDataParallel on gloo + clip_grad_norm_ + torch.optim.AdamW) on the
-box's host cores, fed the same synthetic gradients through autograd.
+box's host cores, on the full parameter set, fed the same kind of synthetic gradients through autograd.
 """
 from __future__ import annotations
 
