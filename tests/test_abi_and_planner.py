@@ -146,3 +146,37 @@ def test_product_has_no_cpu_fallback(native_lib):
             if f.endswith((".py", ".cu", ".cuh")):
                 src = open(os.path.join(root, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src and "libddp_oracle" not in src, f
+
+
+def test_torch_library_ops_are_registered_with_schemas_and_fake_impls(native_lib):
+    """The dispatcher-facing layer (ddp_b200/ops.py) without a GPU: every op exists with the schema the docs
+    state, its fake implementation runs under FakeTensorMode (what torch.compile traces with), and a CPU
+    tensor is refused by the dispatcher — the ops are registered for CUDA only, there is no CPU kernel."""
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    ops = torch.ops.ddp_b200
+    want = {
+        "pack_scale_cast": "(Tensor[] src, Tensor(a1!)[] dst, float scale) -> ()",
+        "pack_scale_cast_sumsq": "(Tensor[] src, Tensor(a1!)[] dst, float scale, Tensor(a3!) sumsq_out) -> ()",
+        "l2norm_sumsq": "(Tensor[] grads, Tensor(a1!) sumsq_out) -> ()",
+        "l2norm_finalize": "(Tensor sumsq, float max_norm, bool torch_bf16) -> Tensor",
+        "scale_by_": "(Tensor(a0!)[] grads, Tensor coef) -> ()",
+    }
+    for name, sig in want.items():
+        assert str(getattr(ops, name).default._schema) == f"ddp_b200::{name}{sig}"
+    adam = str(ops.fused_clip_adamw_.default._schema)
+    assert adam.startswith("ddp_b200::fused_clip_adamw_(Tensor(a0!)[] params, Tensor(a1!)[] grads, Tensor(a2!)[] exp_avgs, "
+                           "Tensor(a3!)[] exp_avg_sqs, float lr, float beta1, float beta2, float weight_decay, float eps, SymInt step")
+    assert "Tensor? clip_coef=None, Tensor? grad_scale=None, Tensor? found_inf=None" in adam
+    assert "Tensor(a0!) arena, Tensor[] views, Tensor(a2!) sumsq_out" in str(ops.allreduce_sumsq_.default._schema)
+    with FakeTensorMode():
+        g = [torch.empty(10, device="cuda", dtype=torch.bfloat16), torch.empty(5, device="cuda", dtype=torch.bfloat16)]
+        ss = torch.empty(2, device="cuda")
+        ops.l2norm_sumsq(g, ss)
+        out = ops.l2norm_finalize(ss, 1.0, True)
+        assert out.shape == (2,) and out.dtype == torch.float32 and out.device.type == "cuda"
+        m = [torch.zeros_like(x) for x in g]
+        ops.fused_clip_adamw_([x.clone() for x in g], g, m, [x.clone() for x in m], 1e-3, 0.9, 0.999, 0.01, 1e-8, 1,
+                              clip_coef=out[1:2])
+        ops.pack_scale_cast(g, [torch.empty_like(x) for x in g], 0.5)
+    with pytest.raises(NotImplementedError):
+        ops.l2norm_sumsq([torch.zeros(4)], torch.zeros(1))
