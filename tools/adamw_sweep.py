@@ -33,11 +33,13 @@ def timeit(fn, reps=10, warm=3):
 
 def run_case(K, dev, peak, name, numel):
     n = sum(numel)
+    DT = torch.bfloat16 if os.environ.get("SWEEP_DTYPE", "f32") == "bf16" else torch.float32
+    B = 14 if DT == torch.bfloat16 else 28            # algorithmic bytes per parameter of the update
     gen = torch.Generator(device=dev).manual_seed(0)
-    p = torch.empty(n, dtype=torch.float32, device=dev).normal_(0, 0.02, generator=gen)
-    g = torch.empty(n, dtype=torch.float32, device=dev).normal_(0, 0.01, generator=gen)
-    m = torch.zeros(n, dtype=torch.float32, device=dev)
-    v = torch.zeros(n, dtype=torch.float32, device=dev)
+    p = torch.empty(n, dtype=DT, device=dev).normal_(0, 0.02, generator=gen)
+    g = torch.empty(n, dtype=DT, device=dev).normal_(0, 0.01, generator=gen)
+    m = torch.zeros(n, dtype=DT, device=dev)
+    v = torch.zeros(n, dtype=DT, device=dev)
 
     def views(t):
         o, r = 0, []
@@ -46,24 +48,25 @@ def run_case(K, dev, peak, name, numel):
             o += k
         return r
 
-    tab = K.table([views(p), views(g), views(m), views(v)], numel, device=dev)
+    tab = K.table([views(p), views(g), views(m), views(v)], numel, chunk_elems=ddp_b200.optim.adamw_chunk_elems(n), device=dev)
+    ntab = K.table([None, views(g), None, None], numel, device=dev)        # the norm keeps the long chunks
     ss = torch.empty(len(numel), dtype=torch.float32, device=dev)
     hp = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2)
     step = [0]
 
     def ours():
         step[0] += 1
-        K.sumsq(tab, torch.float32, ss)
-        coef = K.norm_finalize(ss, 1.0, False)
-        K.adamw(tab, torch.float32, torch.float32, torch.float32, step=step[0], clip_coef=coef[1:2], **hp)
+        K.sumsq(ntab, DT, ss)
+        coef = K.norm_finalize(ss, 1.0, DT == torch.bfloat16)
+        K.adamw(tab, DT, DT, DT, step=step[0], clip_coef=coef[1:2], **hp)
 
     def ours_adam_only():
         step[0] += 1
-        K.adamw(tab, torch.float32, torch.float32, torch.float32, step=step[0], **hp)
+        K.adamw(tab, DT, DT, DT, step=step[0], **hp)
 
     t_ours = timeit(ours)
     t_adam = timeit(ours_adam_only)
-    del tab, m, v                     # torch's optimizer allocates its own state: make room (8 B: 64 GB)
+    del tab, ntab, m, v                     # torch's optimizer allocates its own state: make room (8 B: 64 GB)
     gc.collect()
     torch.cuda.empty_cache()
     ps = [torch.nn.Parameter(x) for x in views(p)]
@@ -78,11 +81,11 @@ def run_case(K, dev, peak, name, numel):
         opt.step()
 
     t_torch = timeit(torch_both)
-    r = dict(case=name, params=n, tensors=len(numel),
-             ours_adamw_ms=t_adam, ours_adamw_gbs=28 * n / t_adam / 1e6, ours_adamw_frac_of_measured_peak=28 * n / t_adam / 1e6 / peak,
-             ours_adamw_frac_of_8000=28 * n / t_adam / 1e6 / 8000,
-             torch_fused_adamw_ms=t_torch_adam, torch_fused_adamw_gbs=28 * n / t_torch_adam / 1e6,
-             ours_norm_clip_adamw_ms=t_ours, ours_path_gbs=32 * n / t_ours / 1e6,
+    r = dict(case=name, dtype=str(DT).replace('torch.', ''), params=n, tensors=len(numel),
+             ours_adamw_ms=t_adam, ours_adamw_gbs=B * n / t_adam / 1e6, ours_adamw_frac_of_measured_peak=B * n / t_adam / 1e6 / peak,
+             ours_adamw_frac_of_8000=B * n / t_adam / 1e6 / 8000,
+             torch_fused_adamw_ms=t_torch_adam, torch_fused_adamw_gbs=B * n / t_torch_adam / 1e6,
+             ours_norm_clip_adamw_ms=t_ours, ours_path_gbs=(B + B // 7) * n / t_ours / 1e6,
              torch_clip_plus_fused_adamw_ms=t_torch, speedup_adamw=t_torch_adam / t_adam, speedup_path=t_torch / t_ours)
     return r
 
