@@ -34,7 +34,10 @@ namespace ddpb200 {
 
 // One chunk through G-element groups (vector accesses); returns how many elements were done, the
 // ragged end is left to the caller's scalar loop.
-template <int PDT, int GDT, int SDT, int MODE, int VECB, bool PACKED>
+// GELEM: the gradient stream alone is not aligned to the group (a bucket view behind an odd-sized tensor of the
+// same bucket, against parameters and state from the allocator): it is read, and in the general mode written,
+// element by element — L1 merges the eight accesses of a group — while p, m and v keep their vector accesses.
+template <int PDT, int GDT, int SDT, int MODE, int VECB, bool PACKED, bool GELEM = false>
 __device__ __forceinline__ int64_t adamw_chunk_vec(char* P, char* Gp, char* M, char* V, int64_t len,
                                                    const AdamScalars& a, const AdamRuntime& r,
                                                    const AdamPacked& pk, bool store_g) {
@@ -44,7 +47,12 @@ __device__ __forceinline__ int64_t adamw_chunk_vec(char* P, char* Gp, char* M, c
 #pragma unroll 1
   for (int64_t i = (int64_t)threadIdx.x * G; i < groups_end; i += kThreads * G) {
     float p[G], g[G], m[G], v[G];
-    GroupIO<GDT, G>::load(Gp, i, g);
+    if constexpr (GELEM) {
+#pragma unroll
+      for (int k = 0; k < G; ++k) g[k] = load1<GDT>(Gp, i + k);
+    } else {
+      GroupIO<GDT, G>::load(Gp, i, g);
+    }
     GroupIO<PDT, G>::load(P, i, p);
     GroupIO<SDT, G>::load(M, i, m);
     GroupIO<SDT, G>::load(V, i, v);
@@ -57,7 +65,14 @@ __device__ __forceinline__ int64_t adamw_chunk_vec(char* P, char* Gp, char* M, c
     GroupIO<PDT, G>::store(P, i, p);
     GroupIO<SDT, G>::store(M, i, m);
     GroupIO<SDT, G>::store(V, i, v);
-    if (MODE == kModeGeneral && store_g) GroupIO<GDT, G>::store(Gp, i, g);
+    if (MODE == kModeGeneral && store_g) {
+      if constexpr (GELEM) {
+#pragma unroll
+        for (int k = 0; k < G; ++k) store1<GDT>(Gp, i + k, g[k]);
+      } else {
+        GroupIO<GDT, G>::store(Gp, i, g);
+      }
+    }
   }
   return groups_end;
 }
@@ -99,6 +114,8 @@ adamw_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t chun
       done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 32, PACKED>(P, Gp, M, V, len, a, r, pk, store_g);
     else if (all_aligned<PDT, GDT, SDT, GroupSize<16, any_f32>::G>(P, Gp, M, V))
       done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 16, PACKED>(P, Gp, M, V, len, a, r, pk, store_g);
+    else if (all_aligned<PDT, GDT, SDT, GroupSize<16, any_f32>::G>(P, P, M, V))          // only the gradient is off
+      done = adamw_chunk_vec<PDT, GDT, SDT, MODE, 16, PACKED, true>(P, Gp, M, V, len, a, r, pk, store_g);
     // ragged end, or a segment whose base is not even 16-byte aligned (odd offset inside a bucket)
     for (int64_t i = done + threadIdx.x; i < len; i += kThreads) {
       float p = load1<PDT>(P, i), g = load1<GDT>(Gp, i), m = load1<SDT>(M, i), v = load1<SDT>(V, i);

@@ -59,7 +59,10 @@ template <int DT> __device__ __forceinline__ void unpack16(const Raw<4>& t, floa
   }
 }
 
-struct BulkChunk { char *P, *G, *M, *V; int64_t len; bool staged; };
+// staged: p, m and v are 16-byte aligned and go through shared memory; g_staged: so does the gradient. A gradient
+// that alone is misaligned (a bucket view behind an odd-sized tensor of the same bucket) is read from global memory
+// element by element by the consumers while the other three streams stay staged.
+struct BulkChunk { char *P, *G, *M, *V; int64_t len; bool staged, g_staged; };
 
 template <int ES, class Tab>
 __device__ __forceinline__ BulkChunk bulk_chunk(const Tab& tab, int64_t c, int64_t chunk_base, int64_t total_chunks,
@@ -73,8 +76,8 @@ __device__ __forceinline__ BulkChunk bulk_chunk(const Tab& tab, int64_t c, int64
   k.G = static_cast<char*>(tab.ptr(s, 1)) + start * ES;
   k.M = static_cast<char*>(tab.ptr(s, 2)) + start * ES;
   k.V = static_cast<char*>(tab.ptr(s, 3)) + start * ES;
-  k.staged = ((reinterpret_cast<uintptr_t>(k.P) | reinterpret_cast<uintptr_t>(k.G) | reinterpret_cast<uintptr_t>(k.M) |
-               reinterpret_cast<uintptr_t>(k.V)) & 15) == 0;
+  k.staged = ((reinterpret_cast<uintptr_t>(k.P) | reinterpret_cast<uintptr_t>(k.M) | reinterpret_cast<uintptr_t>(k.V)) & 15) == 0;
+  k.g_staged = k.staged && (reinterpret_cast<uintptr_t>(k.G) & 15) == 0;
   return k;
 }
 
@@ -113,8 +116,8 @@ adamw_bulk_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t
         mbar_wait(empty + 8 * stage, phase ^ 1);                    // the consumers are done with this slot
         const uint32_t bar = full + 8 * stage, dst = data + stage * kStageBytes;
         if (bytes) {
-          mbar_arrive_expect_tx(bar, 4 * bytes);
-          bulk_g2s(dst, k.G + t0 * ES, bytes, bar);
+          mbar_arrive_expect_tx(bar, (k.g_staged ? 4 : 3) * bytes);
+          if (k.g_staged) bulk_g2s(dst, k.G + t0 * ES, bytes, bar);
           bulk_g2s(dst + kStreamBytes, k.P + t0 * ES, bytes, bar);
           bulk_g2s(dst + 2 * kStreamBytes, k.M + t0 * ES, bytes, bar);
           bulk_g2s(dst + 3 * kStreamBytes, k.V + t0 * ES, bytes, bar);
@@ -141,7 +144,12 @@ adamw_bulk_kernel(const __grid_constant__ Tab tab, int64_t total_chunks, int64_t
       const bool mine = i < vec;
       if (mine) {
         const uint32_t src = data + stage * kStageBytes + threadIdx.x * 16;
-        unpack16<DT>(lds128(src), g);
+        if (k.g_staged) {
+          unpack16<DT>(lds128(src), g);
+        } else {
+#pragma unroll
+          for (int e = 0; e < G; ++e) g[e] = load1<DT>(k.G, t0 + i + e);
+        }
         unpack16<DT>(lds128(src + kStreamBytes), p);
         unpack16<DT>(lds128(src + 2 * kStreamBytes), m);
         unpack16<DT>(lds128(src + 3 * kStreamBytes), v);
