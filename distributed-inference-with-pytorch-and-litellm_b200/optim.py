@@ -203,6 +203,7 @@ class AdamW(Optimizer):
         super().load_state_dict(state_dict)
         self._plan.clear()          # step counts and state tensors were replaced
         self._tables.clear()
+        self._dev_steps_live = False
 
     def _table_for(self, key, plist: List[torch.Tensor], device) -> SegTable:
         """Segment table for this group. Parameter / state pointers never move; gradient pointers
