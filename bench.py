@@ -732,12 +732,9 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "arithmetic": "fp32 opmath on bf16 storage (p, g, exp_avg, exp_avg_sq), as torch's fused AdamW",
             "data": "synthetic", "impl": "ours" + ("-zero1" if zero1 else ""),
-            "config": {"workload": reference_workload_string(args.workload, len(params), total),
-                       "path": f"gradient_as_bucket_view, 25 MiB buckets ({len(bucket_bytes)} after rebuild), "
-                               f"max_norm {MAX_NORM}, AdamW lr {LR}",
-                       "global_batch": f"{ws} replicas x 1 synthetic gradient set",
-                       "l2": f"working set per step {16 * total / 1e9:.1f} GB >> 126 MB L2; no flush needed",
-                       "parallelism": f"dp{ws}" + (" + sharded optimizer (ZeRO-1 style)" if zero1 else "")},
+            "config": workload_config(args.workload, len(params), total, ws),
+            "implementation": f"ddp_b200: gradient_as_bucket_view, {len(bucket_bytes)} buckets after rebuild" +
+                              (", sharded optimizer (ZeRO-1 style)" if zero1 else ""),
             "steps_per_s": args.steps / (ms * 1e-3),
             "e2e": {"value": (ws * e2e_steps / (e2e_ms * 1e-3)) if e2e_steps else None, "unit": UNIT, "steps": e2e_steps,
                     "h2d_bytes_per_step": total * esize, "d2h_bytes_per_step": 8, "numa_local_cpus": numa_cpus,
@@ -936,6 +933,17 @@ def reference_workload_string(workload, n_tensors, total):
     return f"{workload}-arch parameter set, bf16 p/g/m/v, {n_tensors} tensors, {total} elements"
 
 
+def workload_config(workload, n_tensors, total, ws):
+    """The `config` of the JSON line: what is computed, the same dictionary for our arm and for the reference
+    arm (how each arm computes it is said outside `config`)."""
+    return {"workload": reference_workload_string(workload, n_tensors, total),
+            "path": f"DDP gradient sync (25 MiB buckets, averaged over the replicas) + clip_grad_norm_(max_norm {MAX_NORM}) "
+                    f"+ AdamW(lr {LR}, weight_decay 0.01), one step per synthetic gradient set",
+            "global_batch": f"{ws} replicas x 1 synthetic gradient set",
+            "l2": f"working set per step {16 * total / 1e9:.1f} GB >> 126 MB L2; no flush needed",
+            "parallelism": f"dp{ws}"}
+
+
 def cpu_baseline_sample(cfg, total_full):
     """Bounded sample beside our N=1 number: the stock torch CPU path on the FULL parameter set, 5 steps
     after 1 warm-up, every host core. (Runs in a child process: this one already holds an NCCL group.)"""
@@ -995,12 +1003,13 @@ def run_reference(args):
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"], "warmup": r["warmup"],
            "ms_per_step": 1e3 / r["rate"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "bf16", "data": "synthetic", "impl": "reference",
-           "config": {"workload": reference_workload_string(args.workload, len(shapes), total_full),
-                      "parallelism": f"cpu, gloo x{ranks}",
-                      "steps_cap": None if r["steps"] == max(1, args.steps) else
-                                   f"{r['steps']} of the {args.steps} requested steps timed (a step takes {r['warmup_s_per_step']:.1f} s "
-                                   f"with {r['threads']} threads per rank; run bounded to a few minutes)",
-                      "note": note},
+           "config": workload_config(args.workload, len(shapes), total_full, max(1, args.gpus)),
+           "implementation": f"stock torch on the host cores: DistributedDataParallel (gloo, {ranks} rank{'s' if ranks > 1 else ''}) "
+                             f"+ clip_grad_norm_ + torch.optim.AdamW",
+           "steps_cap": None if r["steps"] == max(1, args.steps) else
+                        f"{r['steps']} of the {args.steps} requested steps timed (a step takes {r['warmup_s_per_step']:.1f} s "
+                        f"with {r['threads']} threads per rank; run bounded to a few minutes)",
+           "note": note,
            "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["threads"] * ranks, "kind": "reference", "sample": sample,
                             "host_cpus": os.cpu_count()},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
