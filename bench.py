@@ -1018,9 +1018,9 @@ def run_reference(args):
 
 
 def main():
-    # stdout carries ONE JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION on some boxes) off it
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # stdout carries ONE JSON line: NCCL's own output (the version banner under NCCL_DEBUG=VERSION/WARN, warnings) goes
+    # to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
