@@ -34,6 +34,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# stdout carries ONE JSON line: NCCL's own output (the version banner under NCCL_DEBUG=VERSION, warnings) goes to stderr.
+# Set before torch loads the library.
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 import torch
 import torch.distributed as dist
 
@@ -1018,9 +1022,6 @@ def run_reference(args):
 
 
 def main():
-    # stdout carries ONE JSON line: NCCL's own output (the version banner under NCCL_DEBUG=VERSION/WARN, warnings) goes
-    # to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
