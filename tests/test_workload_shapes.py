@@ -54,3 +54,27 @@ def test_grad_ready_order_and_shapes_match_real_autograd():
         ids = torch.randint(0, 256, (2, 16))
         model(input_ids=ids, labels=ids).loss.backward()
         assert order == bench.grad_ready_order(len(params), 3, tie), tie
+
+
+def test_reference_arm_under_torchrun_prints_one_line_from_rank_0():
+    """`bench.py --impl reference` launched the way the driver launches it at N>1: rank 0 alone works (it drives
+    its own N-rank gloo group on the host cores), the other rank exits 0 without output, and stdout is ONE JSON
+    line with the contract's keys, on the same `config` as our arm would print."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2",
+           "--workload", "tiny", "--steps", "3", "--warmup", "1"]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    lines = [ln for ln in res.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, lines
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["steps"] == 3 and d["warmup"] == 1
+    assert d["gpu_launches"] == 0 and d["vs_baseline"] is None and d["higher_is_better"] is True
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["value"] == d["value"]
+    assert "gloo, 2 ranks" in d["implementation"]
+    assert d["config"] == bench.workload_config("tiny", 20, 1377536, 2)
