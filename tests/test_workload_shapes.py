@@ -3,6 +3,8 @@ configurations (checked against the numel lists recorded from transformers in th
 import json
 import os
 
+import torch
+
 import bench
 
 
@@ -78,3 +80,31 @@ def test_reference_arm_under_torchrun_prints_one_line_from_rank_0():
     assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["value"] == d["value"]
     assert "gloo, 2 ranks" in d["implementation"]
     assert d["config"] == bench.workload_config("tiny", 20, 1377536, 2)
+
+
+def test_parity_metric_of_the_bench_self_check():
+    """bench.parity_check's error measure on CPU tensors: a round-to-nearest result of the fp32 sum is <= 0.5 ulp
+    whatever order the reference was added in, one step off reads as 1.5 (2 across a power of two) at most, and a bf16 running sum — whose
+    error comes from the inputs, not from rounding the result — is far outside; the plain ulp distance, kept for the
+    record, explodes on cancelling inputs while the measure does not blame the result for it."""
+    torch.manual_seed(0)
+    ws, n = 8, 1 << 20
+    xs = [(torch.randn(n) * 0.01 / ws).bfloat16() for _ in range(ws)]
+    fwd, bwd, sumabs = torch.zeros(n), torch.zeros(n), torch.zeros(n)
+    for x in xs:
+        fwd += x.float()
+        sumabs += x.float().abs()
+    for x in reversed(xs):
+        bwd += x.float()
+    rn = fwd.bfloat16()
+    assert bench._err_in_ulps(rn, bwd, sumabs, torch.bfloat16) <= 0.5
+    up = (rn.float() + bench._ulp_of(rn.float(), torch.bfloat16)).bfloat16()
+    # (a step of ulp(rn) taken across a power of two towards zero is two steps of the binade it lands in)
+    assert 0.5 < bench._err_in_ulps(up, bwd, sumabs, torch.bfloat16) <= 2.0 + 1e-3
+    seq = xs[0].clone()
+    for x in xs[1:]:
+        seq = (seq.float() + x.float()).bfloat16()
+    assert bench._err_in_ulps(seq, bwd, sumabs, torch.bfloat16) > 8
+    assert bench._max_ulp(rn, bwd.bfloat16()) <= 1
+    assert bench._ulp_of(torch.tensor([1.0, 0.75, 0.0]), torch.bfloat16).tolist() == [2.0 ** -7, 2.0 ** -8, 2.0 ** -133]
+    assert bench._ulp_of(torch.tensor([1.0]), torch.float32).tolist() == [2.0 ** -23]
