@@ -651,6 +651,29 @@ def run_ours(args):
     launches += 2 * (stats1.get("fused_allreduces", 0) - stats0.get("fused_allreduces", 0))   # allreduce kernel + fold
     allreduces = stats1["allreduces"] - stats0["allreduces"]
 
+    # ---- side figure at N>1: the same step with the buckets launched ONE BY ONE, as the autograd hooks of a real
+    # backward launch them (a collective per 25 MiB-capped bucket instead of one over the whole arena); in training
+    # this path hides behind backward (the `train` record and tools/train_bench.py), here it stands alone
+    per_bucket_ms = None
+    if ws > 1:
+        pb_steps = 5
+
+        def step_per_bucket():
+            ddp.reduce_gradients(None if state["resident"] else grads, order=list(ddp._order))
+            ddp.clip_grad_norm_(MAX_NORM, fused_optimizer=opt)
+            opt.step()
+            if not state["resident"]:
+                opt.zero_grad()
+        step_per_bucket()
+        sync_all()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        for _ in range(pb_steps):
+            step_per_bucket()
+        p1.record()
+        sync_all()
+        per_bucket_ms = p0.elapsed_time(p1) / pb_steps
+
     def run_e2e(e2e_steps):
         # ---- timed: end to end from HOST gradients ---------------------------------------------------
         # Each step's gradients arrive from pinned host memory (H2D inside the timed region) and the
@@ -719,10 +742,10 @@ def run_ours(args):
     else:
         e2e_ms, last_norm = float("nan"), float(ddp._norm_out[0])
 
-    t = torch.tensor([ms, e2e_ms, adamw_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, e2e_ms, adamw_ms, per_bucket_ms or 0.0], dtype=torch.float64, device=dev)
     if ws > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms, adamw_ms = [float(x) for x in t.tolist()]
+    ms, e2e_ms, adamw_ms, per_bucket_ms = [float(x) for x in t.tolist()]
 
     out = None
     if rank == 0:
@@ -763,6 +786,10 @@ def run_ours(args):
         }
         if parity is not None:
             out["parity_check"] = parity
+        if ws > 1:
+            out["per_bucket_path"] = {"ms_per_step": per_bucket_ms, "steps": 5, "buckets": len(bucket_bytes),
+                                      "note": "the same step with one collective per bucket, launched in bucket order as the "
+                                              "autograd hooks of a real backward do; not hidden behind a backward here"}
         if ws > 1:
             # bucket allreduce bus bandwidth, measured alone on the same buckets (NCCL-tests convention)
             out["allreduce"] = measure_allreduce(ddp, ws, dev)
